@@ -1,0 +1,185 @@
+/*
+ * zest_gpu.h -- C ABI of libzest_gpu.so: B200 (sm_100a) implementation of zest's xorb verify / reconstruct
+ * hot path.  Plain pointers and sizes only; no C++ or torch types cross this boundary.
+ *
+ * What it stands in for.  praveer13/zest reaches this arithmetic through the third-party Zig package zig-xet
+ * (module `xet`, build.zig.zon:6-11).  Each entry point below names the reference interface it replaces
+ * (paths relative to the zest repository).  A Zig `extern` block binding these symbols is shown in
+ * INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns ZG_OK (0) or a negative ZG_ERR_*; nothing aborts or throws.  A Zig caller maps a
+ *     non-zero return to an error and takes its existing fallback (parallel -> sequential -> zig-xet,
+ *     src/main.zig:233-256), exactly as it does for a Zig error union today;
+ *   - output buffers are caller-owned, sizes are queried first (no cross-allocator frees; today the callee
+ *     returns an allocator-owned slice that the caller frees, src/xet_bridge.zig:254-258);
+ *   - a context may be used from many threads at once (zest fans out up to 16*8 = 128 tasks per batch,
+ *     src/parallel_download.zig:117,174-182): calls queue for one of the context's lanes (stream + staging);
+ *   - there is no CPU fallback: without a usable CUDA device zg_init fails with ZG_ERR_NO_DEVICE.
+ *   - hashes are 32 raw bytes; their text form is zg_hash_to_hex (four little-endian u64 printed %016x).
+ */
+#ifndef ZEST_GPU_H
+#define ZEST_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define ZG_API __attribute__((visibility("default")))
+#else
+#define ZG_API
+#endif
+
+#define ZG_OK 0
+#define ZG_ERR_INVALID_ARG (-1)
+#define ZG_ERR_CUDA (-2)          /* a CUDA call failed; see zg_last_error()                                 */
+#define ZG_ERR_TRUNCATED (-3)     /* chunk header or payload runs past the end of the blob                    */
+#define ZG_ERR_BAD_HEADER (-4)    /* chunk header version != 0, or scheme 0 with clen != ulen                 */
+#define ZG_ERR_SCHEME (-5)        /* compression scheme other than 0 / 1 / 2 (zig-xet's scheme 3 is rejected) */
+#define ZG_ERR_LZ4_FRAME (-6)     /* bad magic / version / header checksum / dictionary / block size          */
+#define ZG_ERR_LZ4_BLOCK (-7)     /* malformed sequence, offset 0 or outside the window                       */
+#define ZG_ERR_SIZE_MISMATCH (-8) /* decoded size differs from the header's uncompressed_len                  */
+#define ZG_ERR_RANGE (-9)         /* chunk range outside the blob                                             */
+#define ZG_ERR_CAPACITY (-10)     /* caller's output buffer is too small                                      */
+#define ZG_ERR_NO_DEVICE (-11)    /* no CUDA device / driver: this library has no CPU path                    */
+#define ZG_ERR_OOM (-12)          /* device or pinned allocation failed                                       */
+#define ZG_ERR_LIMIT (-13)        /* input exceeds a documented limit of the entry point                      */
+
+typedef struct zg_ctx zg_ctx;
+
+typedef struct zg_opts {
+    uint32_t struct_size; /* sizeof(zg_opts), for forward compatibility                         */
+    uint32_t n_lanes;     /* concurrent calls served at once (streams); 0 = default (4)        */
+    uint64_t reserved[3];
+} zg_opts;
+
+/* ---- life cycle ------------------------------------------------------------------------------------------ */
+
+/* Create a context on CUDA device `device` (one context per GPU; one process per GPU under torchrun).
+ * New: zest has no device state; the nearest analogue is XetBridge.init (src/xet_bridge.zig:54-70). */
+ZG_API int zg_init(int device, const zg_opts* opts, zg_ctx** out);
+ZG_API void zg_shutdown(zg_ctx* ctx);
+ZG_API const char* zg_strerror(int code);
+/* Message of the last failure on the calling thread (empty string if none). */
+ZG_API const char* zg_last_error(void);
+
+/* Pinned host memory the caller can fill directly (network / disk reads land here, then cudaMemcpyAsync).
+ * Replaces the allocator-owned `[]u8` blob of XorbFetchResult.data (src/xet_bridge.zig:45-52). */
+ZG_API int zg_pinned_alloc(zg_ctx* ctx, size_t bytes, void** out);
+ZG_API int zg_pinned_free(zg_ctx* ctx, void* p);
+
+/* ---- host-only helpers (no GPU work) ----------------------------------------------------------------------- */
+
+/* xet.hashing.hashToHex (src/xet_bridge.zig:154, src/server.zig:201-203; pitfall CONTRIBUTING.md:134-136). */
+ZG_API void zg_hash_to_hex(const uint8_t hash[32], char out[65]);
+ZG_API int zg_hex_to_hash(const char* hex, uint8_t out[32]);
+
+/* Walk the [8-byte header][payload] chunk stream of a xorb blob (what XorbReader.init + iteration does,
+ * src/xet_bridge.zig:256).  Arrays may be NULL to count only; otherwise they hold `cap` entries.
+ * hdr_off[i] = byte offset of chunk i's header.  Returns ZG_ERR_CAPACITY if the blob has more than cap chunks. */
+ZG_API int zg_xorb_index(const uint8_t* blob, size_t len, uint32_t cap, uint32_t* n_chunks, uint64_t* hdr_off,
+                  uint32_t* clen, uint32_t* ulen, uint8_t* scheme, uint64_t* total_ulen);
+
+/* Size of extractChunkRange(start, end)'s result, so the caller can allocate. */
+ZG_API int zg_chunk_range_size(const uint8_t* blob, size_t len, uint32_t start, uint32_t end, uint64_t* out_len);
+
+/* ---- the hot path, host buffers in / host buffers out ------------------------------------------------------ */
+
+/* XorbReader.init(alloc, blob).extractChunkRange(start, end) (src/xet_bridge.zig:256-257,
+ * src/parallel_download.zig:65-66): decoded bytes of chunks [start, end), concatenated, into out[0..*out_len).
+ * start/end are relative to the blob actually fetched (XorbFetchResult.local_start/local_end,
+ * src/xet_bridge.zig:45-52). */
+ZG_API int zg_extract_chunk_range(zg_ctx* ctx, const uint8_t* blob, size_t len, uint32_t start, uint32_t end, uint8_t* out,
+                           size_t out_cap, uint64_t* out_len);
+
+/* Verify n whole xorbs: decode every chunk, BLAKE3-keyed chunk hashes, Merkle fold, compare with the content
+ * address.  This is the integrity check zest's README promises (README.md:232,255) and defers to zig-xet
+ * (src/bt_peer.zig:166-169); it belongs right after XetBridge.fetchXorbForTerm returns a full xorb
+ * (src/xet_bridge.zig:149-218) and before XorbCache.put (src/swarm.zig:57-148).
+ *   expected      n x 32 bytes (the xorb hashes = cache keys = term.hash), or NULL to only compute roots
+ *   verdict[i]    1 = root matches, 0 = mismatch, < 0 = ZG_ERR_* of the first chunk that failed to decode
+ *   roots         n x 32 bytes, computed Merkle roots (zeros for a xorb that failed)
+ *   chunk_hashes  optional, chunk_hash_cap x 32 bytes, all xorbs' chunk hashes back to back
+ *   bytes_verified  optional, total uncompressed bytes of the xorbs that decoded */
+ZG_API int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens, const uint8_t* expected, size_t n,
+                    int8_t* verdict, uint8_t* roots, uint8_t* chunk_hashes, size_t chunk_hash_cap,
+                    uint64_t* bytes_verified);
+
+/* Xet chunk hashes (zig-xet hashing; BLAKE3 keyed with the Xet data key) of chunks
+ * data[offsets[i] .. offsets[i+1]), i < n.  key = NULL selects the Xet data key; key = 32 bytes selects another
+ * BLAKE3 key; ZG_PLAIN_BLAKE3 selects unkeyed BLAKE3, which is what `zest bench --synthetic` times
+ * (std.crypto.hash.Blake3, src/bench.zig:207-223). */
+#define ZG_PLAIN_BLAKE3 ((const uint8_t*)(uintptr_t)1)
+ZG_API int zg_hash_chunks(zg_ctx* ctx, const uint8_t* data, const uint64_t* offsets, size_t n, const uint8_t* key,
+                   uint8_t* out_hashes);
+
+/* Merkle root of (hash, length) pairs -- zig-xet hashing's aggregated node hash (CONTRIBUTING.md:144-146).
+ * file_hash != 0 additionally applies the zero-key file-hash step (the value hf_xet.hash_files reports). */
+ZG_API int zg_merkle_root(zg_ctx* ctx, const uint8_t* hashes, const uint64_t* lens, size_t n, int file_hash,
+                   uint8_t out[32]);
+
+/* Gearhash content-defined chunking (zig-xet chunking; parameters src/config.zig:12): chunk END offsets
+ * (exclusive, ascending) of data[0..len).  *n_ends receives the count even when it exceeds cap
+ * (then ZG_ERR_CAPACITY is returned and only cap entries are written). */
+ZG_API int zg_cdc(zg_ctx* ctx, const uint8_t* data, size_t len, uint64_t* ends, size_t cap, size_t* n_ends);
+
+/* Seed path in one call: CDC + chunk hashes (+ optional Xet file hash) -- what feeds storage.writeChunk
+ * (src/storage.zig:102-107).  hashes holds cap x 32 bytes. */
+ZG_API int zg_cdc_hash(zg_ctx* ctx, const uint8_t* data, size_t len, uint64_t* ends, size_t cap, size_t* n_ends,
+                uint8_t* hashes, uint8_t* file_hash /* 32 bytes or NULL */);
+
+/* ---- the same work on device-resident buffers (asynchronous on `stream`, a cudaStream_t) -------------------- */
+/* For callers that already hold the data in HBM (bench.py's device-resident figure, pipelines that overlap
+ * their own copies).  All pointers are device pointers unless noted; buffers must be 16-byte aligned and
+ * readable up to the next multiple of 16.  Scratch is caller-provided (size from the *_scratch_bytes query),
+ * 256-byte aligned; nothing is allocated or synchronised inside these calls. */
+
+typedef struct zg_chunk_desc { /* one per chunk; fill from zg_xorb_index (src_off = hdr_off + 8 + blob base) */
+    uint64_t src_off;          /* payload offset inside the compressed buffer                       */
+    uint64_t dst_off;          /* where the decoded chunk goes inside the output buffer             */
+    uint32_t clen, ulen, scheme, pad;
+} zg_chunk_desc;
+
+ZG_API size_t zg_dev_hash_scratch_bytes(uint64_t data_bytes, size_t n);
+ZG_API int zg_dev_hash_chunks(zg_ctx* ctx, const uint8_t* d_data, uint64_t data_bytes, const uint64_t* d_offsets,
+                       const uint32_t* d_lens /* NULL: lens from offsets[i+1]-offsets[i] */, size_t n,
+                       const uint8_t* key /* host pointer, as zg_hash_chunks */, uint8_t* d_out, void* d_scratch,
+                       size_t scratch_bytes, void* stream);
+
+ZG_API size_t zg_dev_decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes);
+ZG_API int zg_dev_decode_chunks(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes, const zg_chunk_desc* d_chunks,
+                         size_t n_chunks, uint8_t* d_out, uint64_t out_bytes, int32_t* d_status, void* d_scratch,
+                         size_t scratch_bytes, void* stream);
+
+ZG_API size_t zg_dev_merkle_scratch_bytes(size_t n_chunks, size_t n_xorbs);
+/* d_first: n_xorbs + 1 chunk indices delimiting each xorb's chunks in d_hashes / d_lens. */
+ZG_API int zg_dev_merkle(zg_ctx* ctx, const uint8_t* d_hashes, const uint32_t* d_lens, const uint32_t* d_first,
+                  size_t n_xorbs, size_t n_chunks, const int32_t* d_status, const uint8_t* d_expected,
+                  uint8_t* d_roots, int8_t* d_verdict, void* d_scratch, size_t scratch_bytes, void* stream);
+
+/* decode -> hash -> fold -> compare in one call (the three calls above on one stream, sharing scratch). */
+ZG_API size_t zg_dev_verify_scratch_bytes(size_t n_chunks, size_t n_xorbs, uint64_t out_bytes);
+ZG_API int zg_dev_verify_xorbs(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes, const zg_chunk_desc* d_chunks,
+                        size_t n_chunks, const uint32_t* d_first, size_t n_xorbs, const uint8_t* d_expected,
+                        uint64_t out_bytes, uint8_t* d_roots, int8_t* d_verdict, uint8_t* d_chunk_hashes,
+                        void* d_scratch, size_t scratch_bytes, void* stream);
+
+ZG_API size_t zg_dev_cdc_scratch_bytes(uint64_t len);
+/* d_n_out: two u64 {number of cuts, overflow flag}. */
+ZG_API int zg_dev_cdc(zg_ctx* ctx, const uint8_t* d_data, uint64_t len, uint64_t* d_ends, uint64_t cap, uint64_t* d_n_out,
+               void* d_scratch, size_t scratch_bytes, void* stream);
+
+/* ---- statistics -------------------------------------------------------------------------------------------- */
+typedef struct zg_stats {
+    uint64_t calls, kernels_launched, h2d_bytes, d2h_bytes, bytes_decoded, chunks_hashed;
+} zg_stats;
+ZG_API int zg_get_stats(zg_ctx* ctx, zg_stats* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZEST_GPU_H */

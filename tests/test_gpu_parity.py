@@ -1,0 +1,269 @@
+"""Parity of the CUDA path against the oracle and the golden vectors, through the C ABI (zest_b200 -> ctypes ->
+libzest_gpu.so).  Integer / byte work: every comparison is bit-exact.  Run on the B200 box: pytest -m gpu."""
+import hashlib
+
+import numpy as np
+import pytest
+
+import zest_b200 as z
+from conftest import footer_chunk_hashes, golden_input, read_golden_xorb
+
+pytestmark = pytest.mark.gpu
+
+NODE_KEY = bytes([1, 126, 197, 199, 165, 71, 41, 150, 253, 148, 102, 102, 180, 138, 2, 230, 93, 221, 83, 111, 55, 199,
+                  109, 210, 248, 99, 82, 230, 74, 83, 113, 63])
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = z.Context(0)
+    yield c
+    c.close()
+
+
+# ------------------------------------------------------------------------------------------------ BLAKE3 / chunk hash
+def test_blake3_kats(ctx, vectors):
+    for v in vectors["blake3"]:
+        d = bytes([v["fill"]]) * v["len"] if "fill" in v else bytes(i % 251 for i in range(v["len"]))
+        assert z.blake3(d, ctx=ctx).hex() == v["plain"], v["len"]
+        if "data_key" in v:
+            assert z.chunk_hash(d, ctx=ctx).hex() == v["data_key"], v["len"]
+            assert z.hash_chunks(d, [0, len(d)], key=NODE_KEY, ctx=ctx)[0].tobytes().hex() == v["node_key"], v["len"]
+
+
+def test_hello_world(ctx, vectors):
+    rec = next(r for r in vectors["xet"] if r["name"] == "hello_world")
+    assert z.hash_to_hex(z.chunk_hash(b"hello world", ctx=ctx)) == rec["xorb_hash"]
+
+
+@pytest.mark.parametrize("seed,total", [(1, 300_000), (2, 5_000_000), (3, 150_000_000)])
+def test_hash_chunks_vs_oracle(ctx, oracle, seed, total):
+    """Ragged chunkings: empty chunks, 1-byte chunks, leaf/block edge lengths, unaligned starts, every group size."""
+    rng = np.random.default_rng(seed)
+    data = rng.integers(0, 256, total, dtype=np.uint8)
+    edge = [0, 0, 1, 63, 64, 65, 1023, 1024, 1025, 2047, 2048, 2049, 4096, 4097, 8191, 8192, 8193, 16384, 16385,
+            65536, 65537, 131071, 131072, 3, 0, 5000, 12289]
+    lens = list(edge)
+    while sum(lens) < total - 200_000:
+        lens.append(int(rng.integers(0, 131073)))
+    lens.append(total - sum(lens))
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    got = z.hash_chunks(data, off, ctx=ctx)
+    want = oracle.hash_chunks(data, off, threads=8)
+    assert (got == want).all()
+    # a sub-range that starts at an odd offset inside the buffer (offsets[0] != 0)
+    k = len(edge)
+    assert (z.hash_chunks(data, off[k:k + 9], ctx=ctx) == want[k:k + 8]).all()
+
+
+def test_hash_large_chunks(ctx, oracle):
+    """Chunks far above the CDC maximum (the header allows 16 MiB) take the warp-cooperative tree path."""
+    data = np.random.default_rng(9).integers(0, 256, 40_000_000, dtype=np.uint8)
+    off = np.array([0, 16_777_215, 16_777_215 + 3_000_001, 40_000_000], np.uint64)
+    assert (z.hash_chunks(data, off, ctx=ctx) == oracle.hash_chunks(data, off, threads=4)).all()
+    assert z.blake3(data[:20_000_000], ctx=ctx) == oracle.blake3(data[:20_000_000])
+
+
+# ------------------------------------------------------------------------------------------------ Merkle fold
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 4, 5, 8, 9, 10, 17, 100, 1060, 2047, 2048, 2049, 4100, 8192, 20011])
+def test_merkle_vs_oracle(ctx, oracle, n):
+    rng = np.random.default_rng(n)
+    hashes = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    lens = rng.integers(0, 131073, n).astype(np.uint64)
+    assert z.merkle_root(hashes, lens, ctx=ctx) == oracle.merkle_root(hashes, lens)
+    assert z.file_hash(hashes, lens, ctx=ctx) == oracle.file_hash(hashes, lens)
+
+
+def test_merkle_cut_patterns(ctx, oracle):
+    """Force the cut rule's corners: no hash divisible by 4 (groups of 9), all divisible (groups of 3)."""
+    n = 500
+    rng = np.random.default_rng(0)
+    for low in (1, 0):
+        hashes = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        hashes[:, 24] = (hashes[:, 24] & 0xFC) | low
+        lens = rng.integers(1, 10**9, n).astype(np.uint64)
+        assert z.merkle_root(hashes, lens, ctx=ctx) == oracle.merkle_root(hashes, lens)
+
+
+# ------------------------------------------------------------------------------------------------ decode / extract
+@pytest.mark.parametrize("name", ["xorb_bf16", "xorb_text", "xorb_rand", "xorb_mixed_auto", "xorb_tiny"])
+def test_extract_real_xorbs(ctx, oracle, vectors, name):
+    rec = next(r for r in vectors["real_xorbs"] if r["name"] == name)
+    stream, raw = read_golden_xorb(rec)
+    gold_hashes, unc_ends, xorb_hash = footer_chunk_hashes(raw)
+    reader = z.XorbReader.init(stream, ctx)
+    n = rec["n_chunks"]
+    full = reader.extract_chunk_range(0, n)
+    assert full == oracle.extract_chunk_range(stream, 0, n)
+    assert hashlib.sha256(full).hexdigest() == rec["sha256"]
+    for s, e in [(0, 1), (n - 1, n), (1, n), (0, n - 1), (n // 2, n // 2), (n // 3, 2 * n // 3 + 1)]:
+        if 0 <= s <= e <= n:
+            assert reader.extractChunkRange(s, e) == oracle.extract_chunk_range(stream, s, e)
+    res = z.verify_xorbs([stream], [xorb_hash], want_chunk_hashes=True, ctx=ctx)
+    assert res.verdict[0] == 1 and res.roots[0].tobytes() == xorb_hash
+    assert (res.chunk_hashes == gold_hashes).all() and res.bytes_verified == rec["n_bytes"]
+    with pytest.raises(z.ZestGpuError) as ei:
+        reader.extract_chunk_range(0, n + 1)
+    assert ei.value.code == -9
+
+
+GENS = {"text": "synth_zipf_text", "bf16": "synth_bf16", "rand": "synth_random"}
+
+
+@pytest.mark.parametrize("kind,policy,nbytes,block_max", [
+    ("text", 1, 3_000_001, 0), ("text", 1, 1_500_000, 65536), ("text", 2, 900_000, 0), ("bf16", 2, 6_000_000, 0),
+    ("bf16", 1, 1_000_003, 0), ("rand", 1, 1_000_000, 0), ("rand", 0, 777_777, 0), ("bf16", 2, 2_000_000, 4096),
+])
+def test_synthetic_roundtrip(ctx, oracle, kind, policy, nbytes, block_max):
+    data = getattr(oracle, GENS[kind])(nbytes, 31)
+    xs, ends, hashes = oracle.make_xorbs(data, policy, threads=4, block_max=block_max)
+    x = xs[0]
+    out = z.XorbReader(x.blob, ctx).extract_chunk_range(0, x.n_chunks)
+    assert out == data.tobytes()
+    res = z.verify_xorbs([x.blob], [x.expected], want_chunk_hashes=True, ctx=ctx)
+    assert res.verdict[0] == 1 and (res.chunk_hashes == hashes).all() and res.bytes_verified == nbytes
+
+
+def test_special_streams(ctx, oracle):
+    """Long matches (zeros, period-3, period-40), a one-byte file, an empty xorb list, an empty blob."""
+    cases = [np.zeros(300_000, np.uint8), np.tile(np.frombuffer(b"abc", np.uint8), 100_000),
+             np.tile(np.arange(40, dtype=np.uint8), 9000), np.frombuffer(b"x", np.uint8),
+             np.concatenate([np.zeros(70_000, np.uint8), oracle.synth_random(5000, 1), np.zeros(70_000, np.uint8)])]
+    for data in cases:
+        for policy in (1, 2):
+            xs, _, hashes = oracle.make_xorbs(data, policy)
+            out = z.XorbReader(xs[0].blob, ctx).extract_chunk_range(0, xs[0].n_chunks)
+            assert out == data.tobytes()
+            assert z.verify_xorbs([xs[0].blob], [xs[0].expected], ctx=ctx).ok
+    assert z.verify_xorbs([], ctx=ctx).verdict.size == 0
+    r = z.verify_xorbs([b""], [bytes(32)], ctx=ctx)          # zero chunks: root is 32 zero bytes (A.3)
+    assert r.verdict[0] == 1 and r.roots[0].tobytes() == bytes(32)
+
+
+def test_corruption_verdicts_match_oracle(ctx, oracle, vectors):
+    """Bit flips in header, frame and payload; truncation; wrong expected hash: same verdict as the oracle."""
+    blobs, expected = [], []
+    for name in ("xorb_text", "xorb_bf16", "xorb_mixed_auto"):
+        rec = next(r for r in vectors["real_xorbs"] if r["name"] == name)
+        stream, raw = read_golden_xorb(rec)
+        _, _, xh = footer_chunk_hashes(raw)
+        rng = np.random.default_rng(len(stream))
+        blobs.append(stream); expected.append(xh)
+        blobs.append(stream); expected.append(bytes(32))                      # wrong address
+        for pos in [0, 4, 8, 12, 13, 14, 15, 19, 40] + [int(p) for p in rng.integers(0, len(stream), 40)]:
+            b = bytearray(stream)
+            b[pos] ^= 1 << int(rng.integers(0, 8))
+            blobs.append(bytes(b)); expected.append(xh)
+        blobs.append(stream[:-7]); expected.append(xh)
+        blobs.append(stream[:len(stream) // 2]); expected.append(xh)
+    got = z.verify_xorbs(blobs, expected, ctx=ctx)
+    want_v, want_roots, _ = oracle.verify_xorbs(blobs, expected, threads=8)
+    assert list(got.verdict) == list(want_v)
+    ok = want_v >= 0
+    assert (got.roots[ok] == want_roots[ok]).all()
+    assert (got.verdict[0], got.verdict[1]) == (1, 0)
+    assert (got.verdict <= 0).sum() >= len(blobs) - 3 - 6   # nearly every flip is caught (a flip in padding may not be)
+
+
+def test_many_xorbs_batch(ctx, oracle):
+    """A batch that spans several sub-batches and both pipeline lanes, mixed schemes, one corrupt in the middle."""
+    blobs, expected = [], []
+    for i in range(14):
+        kind, policy = [("text", 1), ("bf16", 2), ("rand", 0)][i % 3]
+        data = getattr(oracle, GENS[kind])(60_000_000 if i == 5 else 2_000_000 + 4099 * i, 100 + i)
+        for x in oracle.make_xorbs(data, policy, threads=8)[0]:
+            blobs.append(x.blob); expected.append(x.expected)
+    bad = bytearray(blobs[7]); bad[len(bad) // 3] ^= 0x40; blobs[7] = bytes(bad)
+    got = z.verify_xorbs(blobs, expected, ctx=ctx)
+    want_v, want_roots, want_bytes = oracle.verify_xorbs(blobs, expected, threads=8)
+    assert list(got.verdict) == list(want_v) and got.verdict[7] <= 0
+    assert (got.roots[want_v >= 0] == want_roots[want_v >= 0]).all()
+
+
+# ------------------------------------------------------------------------------------------------ CDC
+@pytest.mark.parametrize("name", ["seed0_1MiB", "seed1_8MiB", "zeros_1MiB", "seed1_next_8191", "seed1_next_8192",
+                                  "bf16_seed2_4MiB", "zipf_seed3_2MiB", "hello_world", "empty"])
+def test_cdc_kats(ctx, oracle, vectors, name):
+    rec = next(r for r in vectors["xet"] if r["name"] == name)
+    data = golden_input(name)
+    ends, hashes, fh = z.cdc_hash(data, ctx=ctx)
+    assert list(ends) == list(oracle.cdc(data))
+    assert z.hash_to_hex(fh) == rec["file_hash"]
+    assert list(z.cdc(data, ctx=ctx)) == list(ends)
+    if rec["xorb_hash"] is not None and rec["n_chunks"] == ends.size:
+        assert list(ends) == rec["chunk_ends"]
+        assert [z.hash_to_hex(h.tobytes()) for h in hashes] == rec["chunk_hashes"]
+        lens = np.diff(np.concatenate([[0], ends])).astype(np.uint64)
+        assert z.hash_to_hex(z.merkle_root(hashes, lens, ctx=ctx)) == rec["xorb_hash"]
+
+
+@pytest.mark.parametrize("n", [1, 63, 64, 8191, 8192, 8193, 32767, 32768, 32769, 131072, 131073, 262144 + 8191, 1_000_003])
+def test_cdc_sizes_vs_oracle(ctx, oracle, n):
+    for gen in (oracle.synth_random, oracle.synth_zipf_text):
+        data = gen(n, n)
+        assert list(z.cdc(data, ctx=ctx)) == list(oracle.cdc(data))
+
+
+def test_cdc_dense_candidates(ctx, oracle):
+    """Adversarial input: a periodic pattern whose windowed hash has its top 16 bits clear at EVERY position, so
+    every byte is a candidate and tiles overflow their hit lists (the 'dense, re-scan' path).  Cuts must still be
+    exact: every chunk is exactly 8192 bytes."""
+    import ctypes as C
+    T = np.array([int(x, 16) for x in __import__("re").findall(r"0x([0-9a-f]{16})ULL", open(
+        __import__("os").path.join(__import__("conftest").ROOT, "include", "zest_gear_table.h")).read())], dtype=np.uint64)
+    assert T.size == 256
+    # two-byte periodic data: h = sum_k T[b_k] << k over the 64-byte window; search (a, b) with top 16 bits zero
+    w_even = np.uint64(sum(1 << k for k in range(0, 64, 2)))
+    w_odd = np.uint64(sum(1 << k for k in range(1, 64, 2)))
+    with np.errstate(over="ignore"):
+        H = T[:, None] * w_even + T[None, :] * w_odd        # last byte a, previous byte b
+    hits = np.argwhere((H >> np.uint64(48)) == 0)
+    found = None
+    for a, b in hits:
+        with np.errstate(over="ignore"):
+            other = T[b] * w_even + T[a] * w_odd
+        if (other >> np.uint64(48)) == 0:
+            found = (a, b); break
+    if found is None:
+        # fall back to a sparse-but-heavy pattern: one phase of the period hits, i.e. every second byte is a candidate
+        a, b = hits[0]
+    else:
+        a, b = found
+    data = np.tile(np.array([b, a], np.uint8), 200_000)
+    data = np.concatenate([oracle.synth_random(50_000, 1), data, oracle.synth_random(50_000, 2)])
+    want = oracle.cdc(data)
+    assert list(z.cdc(data, ctx=ctx)) == list(want)
+    assert (np.diff(want)[2:20] == 8192).all()
+
+
+# ------------------------------------------------------------------------------------------------ full-size properties
+def test_config1_full_size(ctx, vectors):
+    """BASELINE.json configs[0] at full size: 1 GiB random -> 16,741 chunks, hf_xet's file hash (golden)."""
+    rec = next(r for r in vectors["xet"] if r["name"] == "seed0_1GiB")
+    data = golden_input("seed0_1GiB")
+    ends, hashes, fh = z.cdc_hash(data, ctx=ctx)
+    assert ends.size == rec["n_chunks"] and int(ends[-1]) == data.size
+    assert z.hash_to_hex(fh) == rec["file_hash"]
+    # linearity of the batch API: hashing two halves of the chunk list equals hashing the whole
+    off = np.concatenate([[0], ends]).astype(np.uint64)
+    k = ends.size // 2
+    both = np.concatenate([z.hash_chunks(data, off[:k + 1], ctx=ctx), z.hash_chunks(data, off[k:], ctx=ctx)])
+    assert (both == hashes).all()
+
+
+def test_config2_full_size_roundtrip(ctx, oracle):
+    """BASELINE.json configs[1] at full size (~550 MB Zipf text, LZ4): build -> verify all ok -> reconstruct
+    bit-exact -> flip one byte -> exactly that xorb fails."""
+    data = oracle.synth_zipf_text(550_000_000, 2)
+    xs, ends, hashes = oracle.make_xorbs(data, 1, threads=8)
+    blobs = [x.blob for x in xs]
+    res = z.verify_xorbs(blobs, [x.expected for x in xs], want_chunk_hashes=True, ctx=ctx)
+    assert res.ok and res.bytes_verified == data.size and (res.chunk_hashes == hashes).all()
+    pos = 0
+    for x in xs[:2] + xs[-1:]:
+        pass
+    first = z.XorbReader(blobs[0], ctx).extract_chunk_range(0, xs[0].n_chunks)
+    assert first == data[:xs[0].ulen_total].tobytes()
+    bad = bytearray(blobs[3]); bad[len(bad) // 2] ^= 2; blobs[3] = bytes(bad)
+    res2 = z.verify_xorbs(blobs, [x.expected for x in xs], ctx=ctx)
+    assert [int(v == 1) for v in res2.verdict] == [int(i != 3) for i in range(len(xs))]

@@ -1,0 +1,91 @@
+"""CPU-only checks of the product's host side: the C-ABI library loads, exports every declared symbol, and its
+host-only entry points (hex form, chunk-stream walk, range sizing, sharding) agree with the oracle.  No GPU
+compute is called here."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import zest_b200 as z
+from zest_b200 import _native
+from conftest import ROOT, read_golden_xorb
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "zest_gpu.h")).read()
+    declared = re.findall(r"^ZG_API [\w \*]+?\b(zg_\w+)\(", hdr, flags=re.M)
+    assert len(declared) >= 25 and len(set(declared)) == len(declared)
+    assert set(declared) == set(_native.SYMBOLS)
+    L = _native.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+
+
+def test_no_cpu_fallback_without_device():
+    """On a box without a GPU the context must fail loudly (ZG_ERR_NO_DEVICE); with one it must come up."""
+    import torch
+    if torch.cuda.is_available():
+        z.Context(0).close()
+    else:
+        with pytest.raises(z.ZestGpuError) as ei:
+            z.Context(0)
+        assert ei.value.code == -11
+
+
+def test_hex_form_matches_oracle(oracle):
+    rng = np.random.default_rng(3)
+    for _ in range(20):
+        h = rng.integers(0, 256, 32, dtype=np.uint8).tobytes()
+        s = z.hash_to_hex(h)
+        assert s == oracle.hash_to_hex(h)
+        assert z.hex_to_hash(s) == h
+    assert z.hash_to_hex(bytes(range(32)))[:16] == "0706050403020100"
+    with pytest.raises(z.ZestGpuError):
+        z.hex_to_hash("zz" * 32)
+    with pytest.raises(z.ZestGpuError):
+        z.hex_to_hash("00")
+
+
+@pytest.mark.parametrize("name", ["xorb_bf16", "xorb_text", "xorb_rand", "xorb_mixed_auto", "xorb_tiny"])
+def test_index_matches_oracle(oracle, vectors, name):
+    rec = next(r for r in vectors["real_xorbs"] if r["name"] == name)
+    stream, _ = read_golden_xorb(rec)
+    a, b = z.xorb_index(stream), oracle.xorb_index(stream)
+    assert a.n_chunks == b.n == rec["n_chunks"]
+    assert (a.hdr_off == b.hdr_off).all() and (a.clen == b.clen).all() and (a.ulen == b.ulen).all()
+    assert (a.scheme == b.scheme).all() and a.total_ulen == b.total_ulen
+    L = _native.lib()
+    need = C.c_uint64()
+    arr = np.frombuffer(stream, np.uint8)
+    _native.check(L.zg_chunk_range_size(arr.ctypes.data, arr.size, 1 if a.n_chunks > 1 else 0, a.n_chunks, C.byref(need)))
+    assert need.value == int(a.ulen[1 if a.n_chunks > 1 else 0:].sum())
+    assert L.zg_chunk_range_size(arr.ctypes.data, arr.size, 0, a.n_chunks + 1, C.byref(need)) == -9
+    assert L.zg_chunk_range_size(arr.ctypes.data, arr.size, 2, 1, C.byref(need)) == -9
+
+
+def test_walk_errors_match_oracle(oracle, vectors):
+    rec = next(r for r in vectors["real_xorbs"] if r["name"] == "xorb_text")
+    stream, _ = read_golden_xorb(rec)
+    cases = []
+    b = bytearray(stream); b[0] = 7; cases.append(bytes(b))          # version
+    b = bytearray(stream); b[4] = 3; cases.append(bytes(b))          # scheme 3 (FullBitsliceLZ4) rejected
+    cases.append(stream[:-1]); cases.append(stream[:5]); cases.append(stream + b"\x00\x00")
+    b = bytearray(stream); b[4] = 0; cases.append(bytes(b))          # scheme 0 with clen != ulen
+    for c in cases:
+        with pytest.raises(oracle.OracleError) as eo:
+            oracle.xorb_index(c)
+        with pytest.raises(z.ZestGpuError) as ez:
+            z.xorb_index(c)
+        assert ez.value.code == eo.value.code
+    assert z.xorb_index(b"").n_chunks == 0
+
+
+def test_partition_xorbs():
+    sizes = [57, 3, 60, 58, 1, 59, 57, 2, 61]
+    for n in (1, 2, 4, 8):
+        parts = z.partition_xorbs(sizes, n)
+        assert sorted(i for p in parts for i in p) == list(range(len(sizes)))
+        loads = [sum(sizes[i] for i in p) for p in parts]
+        assert max(loads) - min(loads) <= max(sizes)

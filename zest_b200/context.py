@@ -1,0 +1,83 @@
+"""Device context: one per GPU (one process per GPU under torchrun).  Mirrors the role XetBridge plays for zest's
+callers (/root/reference/src/xet_bridge.zig:54-70): the object the verify / reconstruct calls hang off."""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+
+import numpy as np
+
+from . import _native
+from ._native import Stats, check
+
+
+class Context:
+    def __init__(self, device: int = 0, n_lanes: int = 0):
+        L = _native.lib()
+        self._h = C.c_void_p()
+
+        class Opts(C.Structure):
+            _fields_ = [("struct_size", C.c_uint32), ("n_lanes", C.c_uint32), ("reserved", C.c_uint64 * 3)]
+
+        o = Opts(C.sizeof(Opts), n_lanes)
+        check(L.zg_init(device, C.byref(o), C.byref(self._h)))
+        self.device = device
+        self._pinned = {}
+
+    @property
+    def handle(self):
+        if not self._h:
+            raise RuntimeError("context is closed")
+        return self._h
+
+    def close(self):
+        if self._h:
+            for p in list(self._pinned):
+                self.pinned_free(p)
+            _native.lib().zg_shutdown(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # pinned host staging the caller fills directly (zg_pinned_alloc)
+    def pinned_empty(self, nbytes: int) -> np.ndarray:
+        p = C.c_void_p()
+        check(_native.lib().zg_pinned_alloc(self.handle, nbytes, C.byref(p)))
+        buf = (C.c_uint8 * max(nbytes, 1)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=np.uint8, count=nbytes)
+        self._pinned[p.value] = buf
+        return arr
+
+    def pinned_free(self, addr_or_array):
+        addr = addr_or_array.ctypes.data if isinstance(addr_or_array, np.ndarray) else int(addr_or_array)
+        if addr in self._pinned:
+            del self._pinned[addr]
+            check(_native.lib().zg_pinned_free(self.handle, C.c_void_p(addr)))
+
+    def stats(self) -> dict:
+        s = Stats()
+        check(_native.lib().zg_get_stats(self.handle, C.byref(s)))
+        return {n: int(getattr(s, n)) for n, _ in Stats._fields_}
+
+
+_default = {}
+_dlock = threading.Lock()
+
+
+def default_context(device: int = 0) -> Context:
+    """Process-wide context per device, created on first use."""
+    with _dlock:
+        c = _default.get(device)
+        if c is None or not c._h:
+            c = _default[device] = Context(device)
+        return c

@@ -1,0 +1,366 @@
+// Xet chunk hashing on sm_100a: BLAKE3 (keyed or plain) of many variable-length chunks in one pass.
+//
+// Reference behaviour replaced: zig-xet `hashing` (chunk hash = BLAKE3.keyed(DATA_KEY, bytes)), reached from
+// /root/reference/src/xet_bridge.zig:256-257 and src/parallel_download.zig:65-66; plain mode reproduces
+// src/bench.zig:207-223.  Algorithm: SURVEY.md A.2; oracle: oracle/xet_oracle.c (b3_hash).
+//
+// Mapping.  BLAKE3 is a chain of 16 compressions inside every 1 KiB leaf and a binary tree above the leaves, so
+// the parallel unit is the leaf.  One THREAD owns an aligned group of G leaves (G = 1, 2, 4 or 8 KiB of
+// contiguous input), chains the 16 x G block compressions with state and message words in registers, and folds
+// its own complete sub-tree with a small chaining-value stack -- so 32 lanes stay busy through the first log2(G)
+// tree levels.  Group nodes (32 B per G KiB, the only scratch traffic) go to a second, tiny kernel that finishes
+// each chunk's tree with one thread per chunk (lanes stay dense across chunks) or one warp for very large
+// chunks.  Lanes are packed densely over chunks of any size by a prefix sum over groups-per-chunk.
+//
+// Roofline: integer-ALU bound.  A block costs 7 x 8 x 12 + 8 = 680 ALU-pipe instructions (IADD3/LOP3/SHF/PRMT);
+// the input is read exactly once (1 B/B of HBM traffic, >= 4x below the HBM roof at ALU speed).
+#include <cstdio>
+
+#include "kernels.h"
+
+namespace zg {
+
+namespace {
+
+constexpr int kLeaf = 1024;
+constexpr int kTile = 1024;  // chunks per scan tile
+
+__device__ __forceinline__ uint32_t groups_of(uint64_t len, int group_bytes) {
+    return len == 0 ? 1u : (uint32_t)((len + group_bytes - 1) / group_bytes);
+}
+__device__ __forceinline__ uint64_t chunk_len(const uint64_t* off, const uint32_t* len, size_t i) {
+    return len ? (uint64_t)len[i] : off[i + 1] - off[i];
+}
+
+// ---- job set-up: P[i] = first group slot of chunk i (exclusive prefix sum), map[slot] = chunk -------------
+__global__ void __launch_bounds__(kTile) hash_count_kernel(const uint64_t* __restrict__ off,
+                                                           const uint32_t* __restrict__ len, size_t n,
+                                                           int group_bytes, uint32_t* __restrict__ P,
+                                                           uint32_t* __restrict__ tile_sum) {
+    __shared__ uint32_t warp_tot[32];
+    size_t i = (size_t)blockIdx.x * kTile + threadIdx.x;
+    uint32_t m = i < n ? groups_of(chunk_len(off, len, i), group_bytes) : 0u;
+    uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, x = m;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t t = warp_tot[lane], s = t;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, s, d);
+            if (lane >= d) s += y;
+        }
+        warp_tot[lane] = s - t;
+        if (lane == 31) tile_sum[blockIdx.x] = s;
+    }
+    __syncthreads();
+    if (i < n) P[i] = warp_tot[w] + x - m;
+}
+
+__global__ void __launch_bounds__(1024) hash_tiles_kernel(uint32_t* __restrict__ tile_sum, uint32_t n_tiles,
+                                                          uint32_t* __restrict__ total_out) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t carry_s;
+    uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_tiles; base += 1024) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t carry = carry_s;  // stable here: the previous iteration ended with a barrier
+        uint32_t m = i < n_tiles ? tile_sum[i] : 0u, x = m;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+            if (lane >= d) x += y;
+        }
+        if (lane == 31) warp_tot[w] = x;
+        __syncthreads();
+        if (w == 0) {
+            uint32_t t = warp_tot[lane], s = t;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                uint32_t y = __shfl_up_sync(0xffffffffu, s, d);
+                if (lane >= d) s += y;
+            }
+            warp_tot[lane] = s - t;
+            if (lane == 31) carry_s = carry + s;
+        }
+        __syncthreads();
+        if (i < n_tiles) tile_sum[i] = carry + warp_tot[w] + x - m;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total_out = carry_s;
+}
+
+__global__ void __launch_bounds__(256) hash_map_kernel(const uint64_t* __restrict__ off,
+                                                       const uint32_t* __restrict__ len, size_t n, int group_bytes,
+                                                       uint32_t* __restrict__ P,
+                                                       const uint32_t* __restrict__ tile_sum,
+                                                       uint32_t* __restrict__ map) {
+    size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    uint32_t base = P[i] + tile_sum[i / kTile];
+    P[i] = base;
+    uint32_t m = groups_of(chunk_len(off, len, i), group_bytes);
+    for (uint32_t k = 0; k < m; k++) map[base + k] = (uint32_t)i;
+}
+
+// ---- message loads ----------------------------------------------------------------------------------------
+__device__ __forceinline__ void load_block_aligned(const uint8_t* p, uint32_t (&m)[16]) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+    m[0] = a.x; m[1] = a.y; m[2] = a.z; m[3] = a.w;
+    m[4] = b.x; m[5] = b.y; m[6] = b.z; m[7] = b.w;
+    m[8] = c.x; m[9] = c.y; m[10] = c.z; m[11] = c.w;
+    m[12] = d.x; m[13] = d.y; m[14] = d.z; m[15] = d.w;
+}
+
+// Any alignment, any length 0..64; bytes past `blen` read as zero.  Only the 16-byte granules that hold bytes
+// of the block are touched, so nothing outside the (16-byte padded) buffer is read.
+__device__ __noinline__ void load_block_general(const uint8_t* p, uint32_t blen, uint32_t (&m)[16]) {
+    uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    uint32_t s = (uint32_t)(a & 15);
+    const uint4* q = reinterpret_cast<const uint4*>(a - s);
+    uint32_t w[21];
+    uint32_t span = s + blen;  // bytes of the 80-byte window that matter
+#pragma unroll
+    for (int g = 0; g < 5; g++) {
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (blen > 0 && (uint32_t)(16 * g) < span) v = __ldg(q + g);
+        w[4 * g] = v.x; w[4 * g + 1] = v.y; w[4 * g + 2] = v.z; w[4 * g + 3] = v.w;
+    }
+    w[20] = 0;
+    if (s & 8) {
+#pragma unroll
+        for (int i = 0; i < 19; i++) w[i] = w[i + 2];
+    }
+    if (s & 4) {
+#pragma unroll
+        for (int i = 0; i < 18; i++) w[i] = w[i + 1];
+    }
+    uint32_t bs = (s & 3) * 8;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        uint32_t x = __funnelshift_r(w[i], w[i + 1], bs);
+        int valid = (int)blen - 4 * i;
+        uint32_t mask = valid >= 4 ? 0xffffffffu : (valid <= 0 ? 0u : ((1u << (8 * valid)) - 1u));
+        m[i] = x & mask;
+    }
+}
+
+// ---- leaf kernel: one thread = one aligned group of G leaves ------------------------------------------------
+template <int G>
+__global__ void __launch_bounds__(128) hash_leaf_kernel(const uint8_t* __restrict__ data,
+                                                        const uint64_t* __restrict__ off,
+                                                        const uint32_t* __restrict__ len, const B3Key key,
+                                                        const uint32_t* __restrict__ P,
+                                                        const uint32_t* __restrict__ map,
+                                                        const uint32_t* __restrict__ total_slots,
+                                                        uint4* __restrict__ nodes, uint4* __restrict__ out) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= *total_slots) return;
+    uint32_t ci = map[t];
+    uint32_t k = t - P[ci];
+    uint64_t clen = chunk_len(off, len, ci);
+    const uint8_t* base = data + off[ci];
+    uint32_t n_leaves = clen == 0 ? 1u : (uint32_t)((clen + kLeaf - 1) / kLeaf);
+    uint32_t first_leaf = k * G;
+    uint32_t g = n_leaves - first_leaf < (uint32_t)G ? n_leaves - first_leaf : (uint32_t)G;
+    bool single_group = n_leaves <= (uint32_t)G;  // this thread produces the chunk's final hash
+
+    constexpr int kDepth = G == 1 ? 1 : (G == 2 ? 2 : (G == 4 ? 3 : 4));
+    uint32_t stack[kDepth][8];
+    int sp = 0;
+    uint32_t cv[8];
+
+#pragma unroll 1
+    for (uint32_t l = 0; l < g; l++) {
+        uint32_t leaf = first_leaf + l;
+        uint64_t lo = (uint64_t)leaf * kLeaf;
+        uint32_t llen = clen - lo < (uint64_t)kLeaf ? (uint32_t)(clen - lo) : (uint32_t)kLeaf;
+        uint32_t nblk = llen == 0 ? 1u : (llen + 63) / 64;
+        const uint8_t* p = base + lo;
+        bool fast_align = (reinterpret_cast<uintptr_t>(p) & 15) == 0;
+        uint32_t root_leaf = (n_leaves == 1) ? B3_ROOT : 0u;
+#pragma unroll
+        for (int i = 0; i < 8; i++) cv[i] = key.w[i];
+#pragma unroll 1
+        for (uint32_t b = 0; b < nblk; b++) {
+            uint32_t blen = llen - 64 * b < 64 ? llen - 64 * b : 64;
+            uint32_t m[16];
+            if (fast_align && blen == 64) load_block_aligned(p + 64 * b, m);
+            else load_block_general(p + 64 * b, blen, m);
+            uint32_t fl = key.base_flags | (b == 0 ? B3_CHUNK_START : 0u) |
+                          (b == nblk - 1 ? (B3_CHUNK_END | root_leaf) : 0u);
+            b3_compress(cv, m, leaf, 0, blen, fl);
+        }
+        if (G == 1) break;
+        // push, then merge completed sub-trees: after leaf l (count l+1), one merge per trailing zero bit; after
+        // the last leaf of the group, merge everything that is left (right to left).
+        bool last = (l == g - 1);
+        uint32_t cnt = l + 1;
+        while (sp > 0 && (last || (cnt & 1) == 0)) {
+            uint32_t left[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) left[i] = stack[sp - 1][i];
+            sp--;
+            uint32_t fl = key.base_flags | B3_PARENT | ((last && sp == 0 && single_group) ? B3_ROOT : 0u);
+            uint32_t r[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) r[i] = cv[i];
+            b3_parent(cv, key.w, left, r, fl);
+            cnt >>= 1;
+        }
+        if (!last) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) stack[sp][i] = cv[i];
+            sp++;
+        }
+    }
+    uint4* dst = single_group ? (out + 2 * (size_t)ci) : (nodes + 2 * (size_t)t);
+    dst[0] = make_uint4(cv[0], cv[1], cv[2], cv[3]);
+    dst[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
+}
+
+// ---- tree kernel: finish every chunk that has more than one group node -------------------------------------
+__device__ __forceinline__ void load_cv(const uint4* p, uint32_t (&cv)[8]) {
+    uint4 a = p[0], b = p[1];
+    cv[0] = a.x; cv[1] = a.y; cv[2] = a.z; cv[3] = a.w;
+    cv[4] = b.x; cv[5] = b.y; cv[6] = b.z; cv[7] = b.w;
+}
+__device__ __forceinline__ void store_cv(uint4* p, const uint32_t (&cv)[8]) {
+    p[0] = make_uint4(cv[0], cv[1], cv[2], cv[3]);
+    p[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
+}
+
+constexpr uint32_t kSerialMax = 16;  // chunks with up to this many nodes are folded by a single thread
+
+__global__ void __launch_bounds__(128) hash_tree_kernel(const B3Key key, const uint32_t* __restrict__ P, size_t n,
+                                                        uint4* __restrict__ nodes, uint4* __restrict__ out) {
+    uint32_t lane = threadIdx.x & 31;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    size_t ci = warp * 32 + lane;
+    uint32_t base = 0, m = 0;
+    if (ci < n) { base = P[ci]; m = P[ci + 1] - base; }
+
+    if (m >= 2 && m <= kSerialMax) {
+        // incremental left-full tree: push node j, merge once per trailing zero of (j+1); then right-to-left
+        uint32_t stack[5][8];
+        int sp = 0;
+        uint32_t cv[8];
+        for (uint32_t j = 0; j < m; j++) {
+            load_cv(nodes + 2 * (size_t)(base + j), cv);
+            bool last = (j == m - 1);
+            uint32_t cnt = j + 1;
+            while (sp > 0 && (last || (cnt & 1) == 0)) {
+                uint32_t left[8], r[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) { left[i] = stack[sp - 1][i]; r[i] = cv[i]; }
+                sp--;
+                b3_parent(cv, key.w, left, r, key.base_flags | B3_PARENT | ((last && sp == 0) ? B3_ROOT : 0u));
+                cnt >>= 1;
+            }
+            if (!last) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) stack[sp][i] = cv[i];
+                sp++;
+            }
+        }
+        store_cv(out + 2 * ci, cv);
+    }
+
+    // very large chunks: the whole warp folds one chunk level by level, in place in the node array
+    uint32_t big = __ballot_sync(0xffffffffu, m > kSerialMax);
+    while (big) {
+        int src = __ffs(big) - 1;
+        big &= big - 1;
+        uint32_t b0 = __shfl_sync(0xffffffffu, base, src), cnt = __shfl_sync(0xffffffffu, m, src);
+        size_t cj = warp * 32 + src;
+        uint4* nd = nodes + 2 * (size_t)b0;
+        while (cnt > 1) {
+            uint32_t pairs = cnt >> 1;
+            for (uint32_t p0 = 0; p0 < pairs; p0 += 32) {
+                uint32_t p = p0 + lane;
+                uint32_t l[8], r[8], o[8];
+                if (p < pairs) { load_cv(nd + 2 * (size_t)(2 * p), l); load_cv(nd + 2 * (size_t)(2 * p + 1), r); }
+                __syncwarp();
+                if (p < pairs) {
+                    b3_parent(o, key.w, l, r, key.base_flags | B3_PARENT | (cnt == 2 ? B3_ROOT : 0u));
+                    store_cv(nd + 2 * (size_t)p, o);
+                }
+                __syncwarp();
+            }
+            if (cnt & 1) {
+                if (lane == 0) { uint32_t t[8]; load_cv(nd + 2 * (size_t)(cnt - 1), t); store_cv(nd + 2 * (size_t)pairs, t); }
+                __syncwarp();
+            }
+            cnt = pairs + (cnt & 1);
+        }
+        if (lane == 0) { uint32_t t[8]; load_cv(nd, t); store_cv(out + 2 * cj, t); }
+        __syncwarp();
+    }
+}
+
+struct HashLayout {
+    size_t p_off, tiles_off, map_off, nodes_off, total;
+    size_t n_tiles, slots_cap;
+};
+HashLayout hash_layout(uint64_t data_bytes, size_t n, int group) {
+    HashLayout L;
+    L.n_tiles = (n + kTile - 1) / kTile;
+    L.slots_cap = (size_t)(data_bytes / ((uint64_t)kLeaf * group)) + n + 1;
+    size_t o = 0;
+    L.p_off = o; o = align_up(o + (n + 1) * 4, 256);
+    L.tiles_off = o; o = align_up(o + (L.n_tiles + 1) * 4, 256);
+    L.map_off = o; o = align_up(o + L.slots_cap * 4, 256);
+    L.nodes_off = o; o = align_up(o + L.slots_cap * 32, 256);
+    L.total = o;
+    return L;
+}
+
+}  // namespace
+
+int hash_pick_group(uint64_t data_bytes) {
+    // keep >= ~96K threads (148 SMs x ~20 warps) busy; beyond that fold more leaves per thread
+    const uint64_t want = 148ull * 32 * 20;
+    for (int g = 8; g > 1; g >>= 1)
+        if (data_bytes / ((uint64_t)kLeaf * g) >= want) return g;
+    return 1;
+}
+
+size_t hash_scratch_bytes(uint64_t data_bytes, size_t n, int group) { return hash_layout(data_bytes, n, group).total; }
+
+cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const uint64_t* off, const uint32_t* len,
+                               size_t n, const B3Key& key, uint8_t* out, void* scratch, size_t scratch_bytes,
+                               int group, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    if (group != 1 && group != 2 && group != 4 && group != 8) return cudaErrorInvalidValue;
+    HashLayout L = hash_layout(data_bytes, n, group);
+    if (scratch_bytes < L.total || n >= 0xffffffffull || L.slots_cap >= 0xffffffffull) return cudaErrorInvalidValue;
+    uint8_t* sb = static_cast<uint8_t*>(scratch);
+    uint32_t* P = reinterpret_cast<uint32_t*>(sb + L.p_off);
+    uint32_t* tiles = reinterpret_cast<uint32_t*>(sb + L.tiles_off);
+    uint32_t* map = reinterpret_cast<uint32_t*>(sb + L.map_off);
+    uint4* nodes = reinterpret_cast<uint4*>(sb + L.nodes_off);
+    int gb = kLeaf * group;
+    hash_count_kernel<<<(unsigned)L.n_tiles, kTile, 0, st>>>(off, len, n, gb, P, tiles);
+    hash_tiles_kernel<<<1, 1024, 0, st>>>(tiles, (uint32_t)L.n_tiles, P + n);
+    hash_map_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(off, len, n, gb, P, tiles, map);
+    unsigned blocks = (unsigned)((L.slots_cap + 127) / 128);
+    uint4* o4 = reinterpret_cast<uint4*>(out);
+    switch (group) {
+        case 1: hash_leaf_kernel<1><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); break;
+        case 2: hash_leaf_kernel<2><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); break;
+        case 4: hash_leaf_kernel<4><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); break;
+        default: hash_leaf_kernel<8><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); break;
+    }
+    hash_tree_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(key, P, n, nodes, o4);
+    return cudaGetLastError();
+}
+
+}  // namespace zg

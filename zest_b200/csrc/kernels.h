@@ -1,0 +1,62 @@
+// Internal launch interface between the C-ABI layer (api.cu) and the kernel translation units.
+// Everything here is asynchronous on the given stream and allocates nothing: scratch comes from the caller.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+#include "blake3.cuh"
+
+namespace zg {
+
+// Error codes (mirror include/zest_gpu.h; kept numerically identical to the oracle's OZ_ERR_*).
+enum : int {
+    E_OK = 0, E_INVALID = -1, E_CUDA = -2, E_TRUNCATED = -3, E_BAD_HEADER = -4, E_SCHEME = -5, E_LZ4_FRAME = -6,
+    E_LZ4_BLOCK = -7, E_SIZE_MISMATCH = -8, E_RANGE = -9, E_CAPACITY = -10, E_NO_DEVICE = -11, E_OOM = -12,
+    E_LIMIT = -13
+};
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---------------------------------------------------------------------------------------------- hashing
+// Leaves per thread in the leaf kernel (1, 2, 4 or 8), chosen from the batch size: small batches need every
+// leaf on its own thread to fill 148 SMs, large ones amortise the tree by folding 8 KiB per thread.
+int hash_pick_group(uint64_t data_bytes);
+size_t hash_scratch_bytes(uint64_t data_bytes, size_t n_chunks, int group);
+
+// Hash n chunks.  Chunk i = data[off[i] .. off[i] + len_i), len_i = len ? len[i] : off[i+1] - off[i].
+// data must be 16-byte aligned and readable up to the next multiple of 16 past the last chunk.
+// out: n x 32 bytes.  scratch: hash_scratch_bytes(data_bytes, n, group) bytes, 256-byte aligned.
+cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const uint64_t* off, const uint32_t* len,
+                               size_t n, const B3Key& key, uint8_t* out, void* scratch, size_t scratch_bytes,
+                               int group, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------- merkle
+// One fold job per xorb: chunks [first[x], first[x+1]) of hashes/lens -> roots[x]; verdict from status/expected.
+size_t merkle_scratch_bytes(size_t n_chunks_total, size_t n_jobs);
+cudaError_t launch_merkle(const uint8_t* hashes, const uint32_t* lens32, const uint64_t* lens64,
+                          const uint32_t* first, size_t n_jobs, size_t n_chunks_total, const int32_t* chunk_status,
+                          const uint8_t* expected, uint8_t* roots, int8_t* verdict, void* scratch,
+                          size_t scratch_bytes, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------- decode
+struct ChunkDesc {      // one per chunk, built by the host walk (zg_xorb_index) or the device index kernel
+    uint64_t src_off;   // payload offset in the compressed buffer
+    uint64_t dst_off;   // where the decoded bytes go in the output buffer
+    uint32_t clen;
+    uint32_t ulen;
+    uint32_t scheme;    // 0 none, 1 lz4 frame, 2 bg4 + lz4 frame
+    uint32_t pad;
+};
+size_t decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes);
+cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkDesc* chunks, size_t n, uint8_t* out,
+                          uint64_t out_bytes, int32_t* status, void* scratch, size_t scratch_bytes, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------- cdc
+size_t cdc_scratch_bytes(uint64_t len);
+// ends: device array of cap u64; n_out: device u64 {count, status}.
+cudaError_t launch_cdc(const uint8_t* data, uint64_t len, uint64_t* ends, uint64_t cap, uint64_t* n_out,
+                       void* scratch, size_t scratch_bytes, cudaStream_t st);
+
+}  // namespace zg

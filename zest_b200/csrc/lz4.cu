@@ -1,0 +1,395 @@
+// Xorb chunk decode on sm_100a: scheme 0 (stored), 1 (LZ4 frame), 2 (4-way byte-grouped LZ4 frame).
+//
+// Reference behaviour replaced: zig-xet XorbReader.extractChunkRange -- the per-chunk decompress loop that zest
+// runs once per reconstruction term (/root/reference/src/xet_bridge.zig:256-257,
+// src/parallel_download.zig:65-66).  Format: SURVEY.md A.4 / A.4b; oracle: oracle/xet_oracle.c (lz4_frame,
+// lz4_block, oz_decode_chunk), whose checks are mirrored one for one and in the same order so that a malformed
+// chunk gets the same error code on both sides.
+//
+// Mapping.  LZ4 token parsing is serial inside a chunk, and on real Xet data the sequences are tiny (bf16
+// byte-grouped: ~4,100 sequences per 64 KiB chunk, ~8 output bytes each outside the two incompressible planes),
+// so the per-sequence instruction count decides throughput.  A warp therefore works on up to 32 chunks at once:
+//   parse   : LANE c walks the token stream of chunk slot c on its own (no warp-wide work per token) and appends
+//             validated (literal source, destination, literal length, match length, offset) records to a
+//             shared-memory list -- all format and bounds checks happen here, on positions only;
+//   execute : for each slot, LANE s performs sequence s of the list: short literal runs and short matches are
+//             copied by their own lane, long ones (the 16-40 KB incompressible planes, zero runs) by the whole
+//             warp with word-wide, funnel-shifted copies; matches wait on earlier matches of the same batch only
+//             when their source overlaps them (frontier test), so most batches finish in one or two rounds.
+// Chunks are handed out through a global ticket counter, so slots refill as soon as a chunk ends.  Output goes to
+// global memory (a 64 MiB xorb stays resident in the 126 MB L2); byte-group regrouping is done by the warp when a
+// scheme-2 chunk completes, reading the planes back from L2.
+//
+// Roofline: HBM-bound in principle (compressed bytes in + decoded bytes out); in practice bounded by issue slots
+// and L1 wavefronts per sequence.  bench.py reports achieved GB/s over those algorithmic bytes.
+#include "kernels.h"
+
+namespace zg {
+
+namespace {
+
+constexpr int kWarps = 4;          // warps per CTA
+constexpr int kSeqCap = 16;        // records parsed per slot per round
+constexpr uint32_t kShortLit = 16; // literal runs up to this length are copied by their own lane
+constexpr uint32_t kShortMatch = 16;
+constexpr uint32_t kMaxPiece = 65535;
+
+enum : int { ST_IDLE = 0, ST_START, ST_BLOCK_HDR, ST_IN_BLOCK, ST_AFTER_BLOCK, ST_FINISH, ST_EXHAUSTED };
+
+struct Seq {           // 16 bytes
+    uint32_t lit_src;  // literal source, relative to the chunk payload
+    uint32_t dst;      // destination of the literals, relative to the chunk's LZ4 output
+    uint32_t lens;     // literal length | match length << 16
+    uint32_t off;      // match offset (1..65535)
+};
+
+__device__ __forceinline__ uint32_t rd8(const uint8_t* p) { return __ldg(p); }
+__device__ __forceinline__ uint32_t rd32(const uint8_t* p) {
+    return rd8(p) | (rd8(p + 1) << 8) | (rd8(p + 2) << 16) | (rd8(p + 3) << 24);
+}
+__device__ __forceinline__ uint32_t rotl32(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+
+// xxh32 of fewer than 16 bytes (the LZ4 frame descriptor is 2..14 bytes), seed 0.
+__device__ uint32_t xxh32_small(const uint8_t* p, uint32_t len) {
+    const uint32_t P1 = 2654435761u, P2 = 2246822519u, P3 = 3266489917u, P4 = 668265263u, P5 = 374761393u;
+    uint32_t h = P5 + len, i = 0;
+    for (; i + 4 <= len; i += 4) h = rotl32(h + rd32(p + i) * P3, 17) * P4;
+    for (; i < len; i++) h = rotl32(h + rd8(p + i) * P5, 11) * P1;
+    h ^= h >> 15; h *= P2; h ^= h >> 13; h *= P3; h ^= h >> 16;
+    return h;
+}
+
+// Whole-warp copy of non-overlapping ranges, any alignment.  Destination words are written aligned; the source
+// is read as aligned words and funnel-shifted.  Reads stay inside the 4-byte words that hold source bytes.
+template <bool SRC_IS_OUTPUT>
+__device__ __forceinline__ void warp_copy(uint8_t* dst, const uint8_t* src, uint32_t len, uint32_t lane) {
+    uint32_t head = (uint32_t)(-(intptr_t)reinterpret_cast<uintptr_t>(dst)) & 3u;
+    if (head > len) head = len;
+    if (lane < head) dst[lane] = SRC_IS_OUTPUT ? src[lane] : __ldg(src + lane);
+    dst += head; src += head; len -= head;
+    uint32_t nw = len >> 2;
+    uintptr_t sa = reinterpret_cast<uintptr_t>(src);
+    uint32_t sh = (uint32_t)(sa & 3) * 8;
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(sa & ~(uintptr_t)3);
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dst);
+    if (sh == 0) {
+        for (uint32_t k = lane; k < nw; k += 32) dw[k] = SRC_IS_OUTPUT ? sw[k] : __ldg(sw + k);
+    } else {
+        for (uint32_t k = lane; k < nw; k += 32) {
+            uint32_t lo = SRC_IS_OUTPUT ? sw[k] : __ldg(sw + k);
+            uint32_t hi = SRC_IS_OUTPUT ? sw[k + 1] : __ldg(sw + k + 1);
+            dw[k] = __funnelshift_r(lo, hi, sh);
+        }
+    }
+    uint32_t tail = len & 3;
+    if (lane < tail) dst[4 * nw + lane] = SRC_IS_OUTPUT ? src[4 * nw + lane] : __ldg(src + 4 * nw + lane);
+}
+
+// Whole-warp LZ4 match copy with overlap semantics: out[dst+i] = out[dst+i-off].  The valid span doubles each
+// round, so a 128 KiB run of one byte takes 17 rounds.
+__device__ __forceinline__ void warp_match(uint8_t* dst, uint32_t off, uint32_t len, uint32_t lane) {
+    const uint8_t* src = dst - off;
+    uint32_t avail = off;
+    while (len) {
+        uint32_t n = len < avail ? len : avail;
+        warp_copy<true>(dst, src, n, lane);
+        __syncwarp();
+        dst += n; len -= n;
+        avail += n - (n % off);  // keep the distance a multiple of the period
+        if (n % off) break;       // only the final piece can be a partial period
+    }
+}
+
+// out[4j+k] = plane_k[j]  (SURVEY.md A.4).  tmp holds the four planes back to back.
+__device__ __forceinline__ void warp_regroup(uint8_t* out, const uint8_t* tmp, uint32_t n, uint32_t lane) {
+    uint32_t q = n >> 2, r = n & 3;
+    uint32_t p1 = q + (0 < r), p2 = p1 + q + (1 < r), p3 = p2 + q + (2 < r);
+    if ((reinterpret_cast<uintptr_t>(out) & 3) == 0) {
+        uint32_t* o = reinterpret_cast<uint32_t*>(out);
+        for (uint32_t j = lane; j < q; j += 32)
+            o[j] = (uint32_t)tmp[j] | ((uint32_t)tmp[p1 + j] << 8) | ((uint32_t)tmp[p2 + j] << 16) | ((uint32_t)tmp[p3 + j] << 24);
+    } else {
+        for (uint32_t j = lane; j < q; j += 32) {
+            out[4 * j] = tmp[j]; out[4 * j + 1] = tmp[p1 + j]; out[4 * j + 2] = tmp[p2 + j]; out[4 * j + 3] = tmp[p3 + j];
+        }
+    }
+    if (lane == 0) {
+        if (r > 0) out[4 * q] = tmp[q];
+        if (r > 1) out[4 * q + 1] = tmp[p1 + q];
+        if (r > 2) out[4 * q + 2] = tmp[p2 + q];
+    }
+}
+
+__global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* __restrict__ comp,
+                                                                 const ChunkDesc* __restrict__ chunks, uint32_t n_chunks,
+                                                                 uint8_t* out, uint8_t* tmp, int32_t* __restrict__ status,
+                                                                 uint32_t* ticket, uint32_t slots) {
+    __shared__ Seq s_list[kWarps][kSeqCap * 32];
+    __shared__ uint8_t s_cnt[kWarps][32];
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    Seq* list = s_list[wid];
+    uint8_t* cnts = s_cnt[wid];
+
+    // per-slot (per-lane) parser state
+    int state = lane < slots ? ST_IDLE : ST_EXHAUSTED;
+    uint32_t ci = 0, clen = 0, ulen = 0, scheme = 0;
+    const uint8_t* src = nullptr;  // chunk payload
+    uint8_t* lz = nullptr;         // where the LZ4 output goes (final position, or the plane buffer for scheme 2)
+    uint8_t* fin_out = nullptr;    // final position of the chunk
+    uint32_t ip = 0, bend = 0, op = 0, win_lo = 0, blk_op = 0, bmax = 0, fflags = 0;  // fflags: 1 indep, 2 bsum, 4 csum
+    uint32_t p_lit = 0, p_lsrc = 0, p_mlen = 0, p_off = 0;
+    int err = 0;
+
+    for (;;) {
+        // ---- refill idle slots from the ticket counter
+        uint32_t idle = __ballot_sync(0xffffffffu, state == ST_IDLE);
+        if (idle) {
+            uint32_t base = 0;
+            int leader = __ffs(idle) - 1;
+            if ((int)lane == leader) base = atomicAdd(ticket, (uint32_t)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (state == ST_IDLE) {
+                uint32_t t = base + __popc(idle & ((1u << lane) - 1));
+                if (t < n_chunks) {
+                    ChunkDesc d = chunks[t];
+                    ci = t; clen = d.clen; ulen = d.ulen; scheme = d.scheme;
+                    src = comp + d.src_off;
+                    fin_out = out + d.dst_off;
+                    lz = scheme == 2 ? tmp + d.dst_off : fin_out;
+                    ip = 0; op = 0; err = 0; p_lit = p_mlen = 0;
+                    state = ST_START;
+                } else
+                    state = ST_EXHAUSTED;
+            }
+        }
+        if (__all_sync(0xffffffffu, state == ST_EXHAUSTED)) break;
+
+        // ---- parse: every active lane appends up to kSeqCap records for its own chunk
+        uint32_t cnt = 0;
+        bool finished = false;  // chunk complete (ok or error) after this round's records
+        while (cnt < (uint32_t)kSeqCap && state != ST_IDLE && state != ST_EXHAUSTED && !finished) {
+            if (p_lit | p_mlen) {
+                uint32_t l = p_lit < kMaxPiece ? p_lit : kMaxPiece;
+                uint32_t m = (l == p_lit) ? (p_mlen < kMaxPiece ? p_mlen : kMaxPiece) : 0u;
+                Seq e{p_lsrc, op, l | (m << 16), p_off};
+                list[cnt * 32 + (lane ^ cnt)] = e;
+                cnt++;
+                op += l + m; p_lsrc += l; p_lit -= l; p_mlen -= m;
+                continue;
+            }
+            switch (state) {
+                case ST_START: {
+                    if (scheme == 0) {
+                        if (clen != ulen) { err = E_BAD_HEADER; finished = true; break; }
+                        p_lit = ulen; p_lsrc = 0;
+                        state = ST_FINISH;
+                    } else if (scheme <= 2) {
+                        if (clen < 7 || rd32(src) != 0x184D2204u) { err = E_LZ4_FRAME; finished = true; break; }
+                        uint32_t flg = rd8(src + 4), bd = rd8(src + 5);
+                        if ((flg >> 6) != 1 || (flg & 0x02) || (bd & 0x8F) || (flg & 1)) { err = E_LZ4_FRAME; finished = true; break; }
+                        uint32_t bcode = (bd >> 4) & 7;
+                        if (bcode < 4) { err = E_LZ4_FRAME; finished = true; break; }
+                        bmax = 1u << (8 + 2 * bcode);
+                        fflags = ((flg >> 5) & 1) | (((flg >> 4) & 1) << 1) | (((flg >> 2) & 1) << 2);
+                        uint32_t csize = (flg >> 3) & 1;
+                        ip = 6 + (csize ? 8 : 0);
+                        if (clen < ip + 1) { err = E_LZ4_FRAME; finished = true; break; }
+                        if (((xxh32_small(src + 4, ip - 4) >> 8) & 0xFF) != rd8(src + ip)) { err = E_LZ4_FRAME; finished = true; break; }
+                        if (csize && (rd32(src + 6) != ulen || rd32(src + 10) != 0)) { err = E_SIZE_MISMATCH; finished = true; break; }
+                        ip++;
+                        state = ST_BLOCK_HDR;
+                    } else { err = E_SCHEME; finished = true; }
+                    break;
+                }
+                case ST_BLOCK_HDR: {
+                    if (clen - ip < 4) { err = E_LZ4_FRAME; finished = true; break; }
+                    uint32_t bs = rd32(src + ip);
+                    ip += 4;
+                    if (bs == 0) {  // EndMark
+                        if (fflags & 4) {
+                            if (clen - ip < 4) { err = E_LZ4_FRAME; finished = true; break; }
+                            ip += 4;
+                        }
+                        if (op != ulen) err = E_SIZE_MISMATCH;
+                        finished = true;
+                        break;
+                    }
+                    uint32_t raw = bs >> 31;
+                    bs &= 0x7FFFFFFFu;
+                    if (bs > bmax || bs > clen - ip) { err = E_LZ4_FRAME; finished = true; break; }
+                    if (raw) {
+                        if (bs > ulen - op) { err = E_SIZE_MISMATCH; finished = true; break; }
+                        p_lit = bs; p_lsrc = ip;
+                        ip += bs;
+                        blk_op = op + bs;  // stored blocks are not subject to the decoded-size check
+                        state = ST_AFTER_BLOCK;
+                    } else {
+                        blk_op = op;
+                        win_lo = (fflags & 1) ? op : 0u;
+                        bend = ip + bs;
+                        state = ST_IN_BLOCK;
+                    }
+                    break;
+                }
+                case ST_IN_BLOCK: {
+                    if (ip >= bend) { err = E_LZ4_BLOCK; finished = true; break; }
+                    uint32_t tok = rd8(src + ip++);
+                    uint32_t lit = tok >> 4;
+                    bool bad = false;
+                    if (lit == 15) {
+                        uint32_t b;
+                        do {
+                            if (ip >= bend) { bad = true; break; }
+                            b = rd8(src + ip++);
+                            lit += b;
+                        } while (b == 255);
+                    }
+                    if (bad || lit > bend - ip) { err = E_LZ4_BLOCK; finished = true; break; }
+                    if (lit > ulen - op) { err = E_SIZE_MISMATCH; finished = true; break; }
+                    uint32_t lsrc = ip;
+                    ip += lit;
+                    if (ip == bend) {  // last sequence of the block: literals only
+                        p_lit = lit; p_lsrc = lsrc;
+                        state = ST_AFTER_BLOCK;
+                        break;
+                    }
+                    if (bend - ip < 2) { err = E_LZ4_BLOCK; finished = true; break; }
+                    uint32_t off = rd8(src + ip) | (rd8(src + ip + 1) << 8);
+                    ip += 2;
+                    uint32_t ml = tok & 15;
+                    if (ml == 15) {
+                        uint32_t b;
+                        do {
+                            if (ip >= bend) { bad = true; break; }
+                            b = rd8(src + ip++);
+                            ml += b;
+                        } while (b == 255);
+                    }
+                    if (bad) { err = E_LZ4_BLOCK; finished = true; break; }
+                    ml += 4;
+                    uint32_t vop = op + lit;
+                    if (off == 0 || off > vop - win_lo) { err = E_LZ4_BLOCK; finished = true; break; }
+                    if (ml > ulen - vop) { err = E_SIZE_MISMATCH; finished = true; break; }
+                    p_lit = lit; p_lsrc = lsrc; p_mlen = ml; p_off = off;
+                    break;
+                }
+                case ST_AFTER_BLOCK: {  // pending literals of the block have been emitted: op is the block end
+                    if (op - blk_op > bmax && blk_op <= op) { err = E_LZ4_FRAME; finished = true; break; }
+                    if (fflags & 2) {
+                        if (clen - ip < 4) { err = E_LZ4_FRAME; finished = true; break; }
+                        ip += 4;
+                    }
+                    state = ST_BLOCK_HDR;
+                    break;
+                }
+                case ST_FINISH: finished = true; break;
+                default: finished = true; break;
+            }
+        }
+        cnts[lane] = (uint8_t)cnt;
+        __syncwarp();
+
+        // ---- execute: one slot at a time, one record per lane
+        uint32_t active = __ballot_sync(0xffffffffu, cnt > 0 || finished);
+        while (active) {
+            int c = __ffs(active) - 1;
+            active &= active - 1;
+            uint32_t n_rec = cnts[c];
+            const uint8_t* c_src = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(src), c));
+            uint8_t* c_lz = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(lz), c));
+            Seq e{0, 0, 0, 0};
+            if (lane < n_rec) e = list[lane * 32 + ((uint32_t)c ^ lane)];
+            uint32_t lit = e.lens & 0xffffu, ml = e.lens >> 16;
+            uint8_t* d = c_lz + e.dst;
+            // literals
+            if (lit && lit <= kShortLit) {
+                const uint8_t* s = c_src + e.lit_src;
+                for (uint32_t b = 0; b < lit; b++) d[b] = __ldg(s + b);
+            }
+            uint32_t longlit = __ballot_sync(0xffffffffu, lit > kShortLit);
+            while (longlit) {
+                int l = __ffs(longlit) - 1;
+                longlit &= longlit - 1;
+                uint32_t l_src = __shfl_sync(0xffffffffu, e.lit_src, l), l_dst = __shfl_sync(0xffffffffu, e.dst, l),
+                         l_len = __shfl_sync(0xffffffffu, lit, l);
+                warp_copy<false>(c_lz + l_dst, c_src + l_src, l_len, lane);
+            }
+            __syncwarp();
+            // matches, in order where they depend on each other
+            uint8_t* md = d + lit;
+            uint32_t m_dst = e.dst + lit;                 // relative start of this lane's match output
+            uint32_t m_src_end = m_dst - e.off + ml;      // relative end of its source range
+            uint32_t pending = __ballot_sync(0xffffffffu, ml > 0);
+            while (pending) {
+                int f = __ffs(pending) - 1;
+                uint32_t f_ml = __shfl_sync(0xffffffffu, ml, f);
+                if (f_ml > kShortMatch) {
+                    uint32_t f_dst = __shfl_sync(0xffffffffu, m_dst, f), f_off = __shfl_sync(0xffffffffu, e.off, f);
+                    warp_match(c_lz + f_dst, f_off, f_ml, lane);
+                    pending &= pending - 1;
+                    __syncwarp();
+                    continue;
+                }
+                uint32_t frontier = __shfl_sync(0xffffffffu, m_dst, f);
+                bool go = ((pending >> lane) & 1) && ml <= kShortMatch && ((int)lane == f || m_src_end <= frontier);
+                if (go) {
+                    const uint8_t* ms = md - e.off;
+                    for (uint32_t b = 0; b < ml; b++) md[b] = ms[b];
+                }
+                __syncwarp();
+                pending &= ~__ballot_sync(0xffffffffu, go);
+            }
+            // chunk finished in this round: regroup (scheme 2) and publish its status
+            uint32_t c_done = __shfl_sync(0xffffffffu, (uint32_t)finished, c);
+            if (c_done) {
+                int c_err = __shfl_sync(0xffffffffu, err, c);
+                uint32_t c_scheme = __shfl_sync(0xffffffffu, scheme, c);
+                if (c_err == 0 && c_scheme == 2) {
+                    uint8_t* c_out = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(fin_out), c));
+                    uint32_t c_ulen = __shfl_sync(0xffffffffu, ulen, c);
+                    warp_regroup(c_out, c_lz, c_ulen, lane);
+                }
+            }
+            __syncwarp();
+        }
+        if (finished) {
+            if (state != ST_FINISH || err) { /* LZ4 chunks validated op == ulen at the EndMark */ }
+            else if (op != ulen) err = E_SIZE_MISMATCH;
+            status[ci] = err;
+            state = ST_IDLE;
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace
+
+size_t decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes) {
+    (void)n_chunks;
+    return 256 + align_up((size_t)out_bytes + 16, 256);  // ticket counter + plane buffer for scheme-2 chunks
+}
+
+cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkDesc* chunks, size_t n, uint8_t* out,
+                          uint64_t out_bytes, int32_t* status, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+    (void)comp_bytes;
+    if (n == 0) return cudaSuccess;
+    if (scratch_bytes < decode_scratch_bytes(n, out_bytes) || n >= 0xffffffffull) return cudaErrorInvalidValue;
+    uint8_t* sb = static_cast<uint8_t*>(scratch);
+    uint32_t* ticket = reinterpret_cast<uint32_t*>(sb);
+    uint8_t* tmp = sb + 256;
+    cudaError_t e = cudaMemsetAsync(ticket, 0, 256, st);
+    if (e != cudaSuccess) return e;
+    // slots per warp: enough warps to give every SM several, at most 32 chunks per warp
+    size_t want_warps = 148 * 8;
+    uint32_t slots = (uint32_t)((n + want_warps - 1) / want_warps);
+    if (slots < 1) slots = 1;
+    if (slots > 32) slots = 32;
+    size_t warps = (n + slots - 1) / slots;
+    size_t max_warps = 148 * 16;
+    if (warps > max_warps) warps = max_warps;
+    unsigned blocks = (unsigned)((warps + kWarps - 1) / kWarps);
+    lz4_decode_kernel<<<blocks, kWarps * 32, 0, st>>>(comp, chunks, (uint32_t)n, out, tmp, status, ticket, slots);
+    return cudaGetLastError();
+}
+
+}  // namespace zg
