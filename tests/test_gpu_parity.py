@@ -36,7 +36,7 @@ def test_hello_world(ctx, vectors):
     assert z.hash_to_hex(z.chunk_hash(b"hello world", ctx=ctx)) == rec["xorb_hash"]
 
 
-@pytest.mark.parametrize("seed,total", [(1, 300_000), (2, 5_000_000), (3, 150_000_000)])
+@pytest.mark.parametrize("seed,total", [(1, 1_200_000), (2, 5_000_000), (3, 150_000_000)])
 def test_hash_chunks_vs_oracle(ctx, oracle, seed, total):
     """Ragged chunkings: empty chunks, 1-byte chunks, leaf/block edge lengths, unaligned starts, every group size."""
     rng = np.random.default_rng(seed)
@@ -205,35 +205,36 @@ def test_cdc_sizes_vs_oracle(ctx, oracle, n):
 
 
 def test_cdc_dense_candidates(ctx, oracle):
-    """Adversarial input: a periodic pattern whose windowed hash has its top 16 bits clear at EVERY position, so
-    every byte is a candidate and tiles overflow their hit lists (the 'dense, re-scan' path).  Cuts must still be
-    exact: every chunk is exactly 8192 bytes."""
-    import ctypes as C
-    T = np.array([int(x, 16) for x in __import__("re").findall(r"0x([0-9a-f]{16})ULL", open(
-        __import__("os").path.join(__import__("conftest").ROOT, "include", "zest_gear_table.h")).read())], dtype=np.uint64)
+    """Adversarial input: a period-4 pattern whose windowed hash has its top 16 bits clear at one phase, so every
+    fourth byte is a candidate (8,192 per 32 KiB tile) and tiles overflow their hit lists -- the 'dense, re-scan'
+    path of the walker.  Cuts must still be exact."""
+    import os
+    import re
+    from conftest import ROOT
+    T = np.array([int(x, 16) for x in re.findall(r"0x([0-9a-f]{16})ULL", open(os.path.join(ROOT, "include", "zest_gear_table.h")).read())],
+                 dtype=np.uint64)
     assert T.size == 256
-    # two-byte periodic data: h = sum_k T[b_k] << k over the 64-byte window; search (a, b) with top 16 bits zero
-    w_even = np.uint64(sum(1 << k for k in range(0, 64, 2)))
-    w_odd = np.uint64(sum(1 << k for k in range(1, 64, 2)))
-    with np.errstate(over="ignore"):
-        H = T[:, None] * w_even + T[None, :] * w_odd        # last byte a, previous byte b
-    hits = np.argwhere((H >> np.uint64(48)) == 0)
+    w = [np.uint64(sum(1 << k for k in range(j, 64, 4))) for j in range(4)]   # weight of the byte j steps back
     found = None
-    for a, b in hits:
-        with np.errstate(over="ignore"):
-            other = T[b] * w_even + T[a] * w_odd
-        if (other >> np.uint64(48)) == 0:
-            found = (a, b); break
-    if found is None:
-        # fall back to a sparse-but-heavy pattern: one phase of the period hits, i.e. every second byte is a candidate
-        a, b = hits[0]
-    else:
-        a, b = found
-    data = np.tile(np.array([b, a], np.uint8), 200_000)
-    data = np.concatenate([oracle.synth_random(50_000, 1), data, oracle.synth_random(50_000, 2)])
+    with np.errstate(over="ignore"):
+        for a in range(256):
+            for b in range(0, 256, 5):
+                H = T[a] * w[0] + T[b] * w[1] + (T[:, None] * w[2] + T[None, :] * w[3])
+                hit = np.argwhere((H >> np.uint64(48)) == 0)
+                if hit.size:
+                    found = (a, b, int(hit[0][0]), int(hit[0][1]))
+                    break
+            if found:
+                break
+    assert found, "no period-4 pattern found"
+    a, b, c, d = found                                    # newest byte a, then b, c, d going back
+    pat = np.array([d, c, b, a], np.uint8)
+    data = np.concatenate([oracle.synth_random(50_001, 1), np.tile(pat, 150_000), oracle.synth_random(70_000, 2),
+                           np.tile(pat, 20_000), oracle.synth_random(9_000, 3)])
     want = oracle.cdc(data)
+    lens = np.diff(np.concatenate([[0], want]))
+    assert (lens[2:40] < 8200).sum() > 20                 # the pattern really does cut at the minimum size
     assert list(z.cdc(data, ctx=ctx)) == list(want)
-    assert (np.diff(want)[2:20] == 8192).all()
 
 
 # ------------------------------------------------------------------------------------------------ full-size properties
