@@ -1,0 +1,139 @@
+#!/usr/bin/env python
+"""Developer tool: time the decode / hash / merkle / cdc kernels alone on one workload, optionally sweeping the
+decode kernel's tuning knobs.  Not part of the product or of bench.py's contract.
+  python tools/stage_bench.py --workload gpt2-lz4 --bytes 550000000 --sweep "1,2,4,8,16,32"
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+import zest_b200 as z  # noqa: E402
+from zest_b200 import _native  # noqa: E402
+from zest_b200._native import ChunkDesc, check  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="gpt2-lz4")
+    ap.add_argument("--bytes", type=int, default=0)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--sweep", default="")
+    ap.add_argument("--warps", default="")
+    ap.add_argument("--cdc", action="store_true")
+    args = ap.parse_args()
+    nbytes = args.bytes or bench.WORKLOADS[args.workload]["nbytes"]
+    dev = torch.device("cuda", 0)
+    ctx = z.Context(0)
+    L = _native.lib()
+    t0 = time.time()
+    blobs, expected, gold, total, nchunks = bench.make_workload(args.workload, nbytes, 1, os.cpu_count())
+    print(f"workload {args.workload}: {total/1e6:.0f} MB, {len(blobs)} xorbs, {nchunks} chunks, ratio {sum(map(len, blobs))/total:.3f}, built in {time.time()-t0:.1f}s", flush=True)
+    nx = len(blobs)
+    descs = (ChunkDesc * nchunks)()
+    first = np.zeros(nx + 1, np.uint32)
+    comp = np.zeros(sum(len(b) for b in blobs) + 16 * nx + 64, np.uint8)
+    cpos = dpos = k = 0
+    for i, b in enumerate(blobs):
+        ix = z.xorb_index(b)
+        first[i] = k
+        comp[cpos:cpos + len(b)] = np.frombuffer(b, np.uint8)
+        for j in range(ix.n_chunks):
+            d = descs[k]
+            d.src_off, d.dst_off, d.clen, d.ulen, d.scheme = cpos + int(ix.hdr_off[j]) + 8, dpos, int(ix.clen[j]), int(ix.ulen[j]), int(ix.scheme[j])
+            dpos += (int(ix.ulen[j]) + 15) // 16 * 16
+            k += 1
+        cpos += (len(b) + 15) // 16 * 16
+    first[nx] = k
+    out_bytes = dpos
+    comp_bytes = sum(len(b) for b in blobs)
+    d_comp = torch.from_numpy(comp).to(dev)
+    d_desc = torch.from_numpy(np.frombuffer(descs, np.uint8).copy()).to(dev)
+    d_first = torch.from_numpy(first.view(np.uint8).copy()).to(dev)
+    d_exp = torch.from_numpy(expected.reshape(-1)).to(dev)
+    off = np.array([d.dst_off for d in descs], np.uint64)
+    lens = np.array([d.ulen for d in descs], np.uint32)
+    d_off, d_len = torch.from_numpy(off.view(np.uint8).copy()).to(dev), torch.from_numpy(lens.view(np.uint8).copy()).to(dev)
+    d_out = torch.zeros(out_bytes + 16, dtype=torch.uint8, device=dev)
+    d_status = torch.zeros(nchunks, dtype=torch.int32, device=dev)
+    d_hashes = torch.zeros(32 * nchunks, dtype=torch.uint8, device=dev)
+    d_roots = torch.zeros(32 * nx, dtype=torch.uint8, device=dev)
+    d_verdict = torch.zeros(nx, dtype=torch.int8, device=dev)
+    s_dec = torch.empty(L.zg_dev_decode_scratch_bytes(nchunks, out_bytes), dtype=torch.uint8, device=dev)
+    s_hash = torch.empty(L.zg_dev_hash_scratch_bytes(out_bytes, nchunks), dtype=torch.uint8, device=dev)
+    s_mer = torch.empty(L.zg_dev_merkle_scratch_bytes(nchunks, nx), dtype=torch.uint8, device=dev)
+    sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def k_decode():
+        check(L.zg_dev_decode_chunks(ctx.handle, d_comp.data_ptr(), cpos, d_desc.data_ptr(), nchunks, d_out.data_ptr(), out_bytes,
+                                     d_status.data_ptr(), s_dec.data_ptr(), s_dec.numel(), sp))
+
+    def k_hash():
+        check(L.zg_dev_hash_chunks(ctx.handle, d_out.data_ptr(), out_bytes, d_off.data_ptr(), d_len.data_ptr(), nchunks, None,
+                                   d_hashes.data_ptr(), s_hash.data_ptr(), s_hash.numel(), sp))
+
+    def k_merkle():
+        check(L.zg_dev_merkle(ctx.handle, d_hashes.data_ptr(), d_len.data_ptr(), d_first.data_ptr(), nx, nchunks, d_status.data_ptr(),
+                              d_exp.data_ptr(), d_roots.data_ptr(), d_verdict.data_ptr(), s_mer.data_ptr(), s_mer.numel(), sp))
+
+    def timed(fn, steps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    def check_all():
+        k_decode(); k_hash(); k_merkle()
+        torch.cuda.synchronize()
+        ok = int(d_status.abs().sum()) == 0 and bool((d_verdict == 1).all()) and np.array_equal(d_hashes.cpu().numpy().reshape(-1, 32), gold)
+        return ok
+
+    res = {}
+    sweeps = [s for s in args.sweep.split(",") if s] or [""]
+    warps = [w for w in args.warps.split(",") if w] or [""]
+    for w in warps:
+        for s in sweeps:
+            os.environ.pop("ZEST_LZ4_SLOTS", None); os.environ.pop("ZEST_LZ4_WARPS", None)
+            if s:
+                os.environ["ZEST_LZ4_SLOTS"] = s
+            if w:
+                os.environ["ZEST_LZ4_WARPS"] = w
+            d_out.zero_()
+            ok = check_all()
+            ms = timed(k_decode, args.steps)
+            print(f"decode slots={s or 'auto':>4} warps={w or 'auto':>5}: {ms:8.3f} ms  {total/ms/1e6:8.1f} GB/s uncompressed  {(total+comp_bytes)/ms/1e6:8.1f} GB/s alg  parity={'ok' if ok else 'FAIL'}", flush=True)
+            res[f"decode_s{s}_w{w}"] = ms
+    os.environ.pop("ZEST_LZ4_SLOTS", None); os.environ.pop("ZEST_LZ4_WARPS", None)
+    ms = timed(k_hash, args.steps)
+    print(f"hash   : {ms:8.3f} ms  {total/ms/1e6:8.1f} GB/s")
+    ms = timed(k_merkle, args.steps)
+    print(f"merkle : {ms:8.3f} ms")
+    if args.cdc:
+        raw = torch.from_numpy(np.frombuffer(getattr(__import__('oracle.xet_oracle', fromlist=['x']), bench.WORKLOADS[args.workload]['gen'])(min(total, 1 << 30), 5), np.uint8).copy()).to(dev)
+        n = raw.numel()
+        cap = n // 8192 + 2
+        d_ends = torch.zeros(cap, dtype=torch.int64, device=dev)
+        d_n = torch.zeros(2, dtype=torch.int64, device=dev)
+        s_cdc = torch.empty(L.zg_dev_cdc_scratch_bytes(n), dtype=torch.uint8, device=dev)
+        f = lambda: check(L.zg_dev_cdc(ctx.handle, raw.data_ptr(), n, d_ends.data_ptr(), cap, d_n.data_ptr(), s_cdc.data_ptr(), s_cdc.numel(), sp))
+        ms = timed(f, args.steps)
+        print(f"cdc    : {ms:8.3f} ms  {n/ms/1e6:8.1f} GB/s  ({int(d_n[0])} chunks)")
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -49,12 +49,14 @@ B3Key make_key(const uint8_t* key) {
                                 0x510E527Fu, 0x9B05688Cu, 0x1F83D9ABu, 0x5BE0CD19u};
         memcpy(k.w, iv, 32);
         k.base_flags = 0;
+        k.one = 1;
         return k;
     }
     const uint8_t* p = key ? key : kDataKey;
     for (int i = 0; i < 8; i++)
         k.w[i] = (uint32_t)p[4 * i] | ((uint32_t)p[4 * i + 1] << 8) | ((uint32_t)p[4 * i + 2] << 16) | ((uint32_t)p[4 * i + 3] << 24);
     k.base_flags = B3_KEYED;
+    k.one = 1;
     return k;
 }
 

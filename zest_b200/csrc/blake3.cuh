@@ -24,16 +24,22 @@ __device__ __forceinline__ uint32_t rotr8(uint32_t x) { return __byte_perm(x, 0,
 __device__ __forceinline__ uint32_t rotr12(uint32_t x) { return __funnelshift_r(x, x, 12); }
 __device__ __forceinline__ uint32_t rotr7(uint32_t x) { return __funnelshift_r(x, x, 7); }
 
-#define ZG_B3_G(a, b, c, d, mx, my) \
-    do {                            \
-        a = a + b + (mx);           \
-        d = rotr16(d ^ a);          \
-        c = c + d;                  \
-        b = rotr12(b ^ c);          \
-        a = a + b + (my);           \
-        d = rotr8(d ^ a);           \
-        c = c + d;                  \
-        b = rotr7(b ^ c);           \
+// The integer ALU pipe (IADD3 / LOP3 / SHF / PRMT, 16 lanes/clk/SMSP) is the bound: ncu shows it ~82 % busy with the
+// FMA pipe ~9 % busy when every add is an IADD3.  IMAD runs on the FMA pipe at the same rate, so the adds are written
+// as x * one + y with `one` an opaque kernel parameter (ptxas folds a literal 1 back into IADD3).  a + b + m becomes
+// (a + m) + b: the first IMAD is off the dependency chain (a is old by then), the second replaces the IADD3.
+// Per G: 8 ALU-pipe + 6 FMA-pipe instructions instead of 10 + 2.
+#define ZG_B3_ADD(x, y) (FMA_ADDS ? ((x) * one + (y)) : ((x) + (y)))
+#define ZG_B3_G(a, b, c, d, mx, my)              \
+    do {                                         \
+        a = ZG_B3_ADD(ZG_B3_ADD(a, (mx)), b);    \
+        d = rotr16(d ^ a);                       \
+        c = ZG_B3_ADD(c, d);                     \
+        b = rotr12(b ^ c);                       \
+        a = ZG_B3_ADD(ZG_B3_ADD(a, (my)), b);    \
+        d = rotr8(d ^ a);                        \
+        c = ZG_B3_ADD(c, d);                     \
+        b = rotr7(b ^ c);                        \
     } while (0)
 
 // One round with message words addressed through the round's schedule s0..s15 (compile-time).
@@ -48,8 +54,10 @@ __device__ __forceinline__ uint32_t rotr7(uint32_t x) { return __funnelshift_r(x
     ZG_B3_G(v3, v4, v9, v14, m[s14], m[s15]);
 
 // cv <- compress(cv, m, counter, block_len, flags); only the 8-word chaining value is produced.
+// `one` must hold 1 at run time (see above); FMA_ADDS = false gives the plain-add form.
+template <bool FMA_ADDS = true>
 __device__ __forceinline__ void b3_compress(uint32_t (&cv)[8], const uint32_t (&m)[16], uint32_t counter_lo,
-                                            uint32_t counter_hi, uint32_t block_len, uint32_t flags) {
+                                            uint32_t counter_hi, uint32_t block_len, uint32_t flags, uint32_t one = 1) {
     uint32_t v0 = cv[0], v1 = cv[1], v2 = cv[2], v3 = cv[3], v4 = cv[4], v5 = cv[5], v6 = cv[6], v7 = cv[7];
     uint32_t v8 = 0x6A09E667u, v9 = 0xBB67AE85u, v10 = 0x3C6EF372u, v11 = 0xA54FF53Au;
     uint32_t v12 = counter_lo, v13 = counter_hi, v14 = block_len, v15 = flags;
@@ -73,12 +81,13 @@ __device__ __forceinline__ void b3_parent(uint32_t (&out)[8], const uint32_t (&k
     for (int i = 0; i < 8; i++) { m[i] = l[i]; m[8 + i] = r[i]; }
 #pragma unroll
     for (int i = 0; i < 8; i++) out[i] = key[i];
-    b3_compress(out, m, 0, 0, 64, flags);
+    b3_compress<false>(out, m, 0, 0, 64, flags);
 }
 
 struct B3Key {
     uint32_t w[8];
     uint32_t base_flags;  // B3_KEYED for the Xet hashes, 0 for plain BLAKE3 (w = IV)
+    uint32_t one;         // always 1: the opaque multiplier that keeps the adds on the FMA pipe (see ZG_B3_ADD)
 };
 
 }  // namespace zg

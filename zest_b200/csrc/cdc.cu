@@ -129,43 +129,67 @@ struct Walker {
     }
 };
 
+__device__ __forceinline__ void load_tile_rec(const TileRec* __restrict__ tiles, uint64_t t, uint64_t n_tiles, uint4& a, uint4& b) {
+    a = make_uint4(0, 0, 0, 0);
+    b = a;
+    if (t < n_tiles) {
+        const uint4* q = reinterpret_cast<const uint4*>(tiles + t);
+        a = __ldg(q);
+        b = __ldg(q + 1);
+    }
+}
+
 __global__ void __launch_bounds__(32) cdc_walk_kernel(const uint8_t* __restrict__ data, uint64_t len,
                                                       const TileRec* __restrict__ tiles, uint64_t n_tiles,
                                                       uint64_t* __restrict__ ends, uint64_t cap,
                                                       uint64_t* __restrict__ n_out) {
+    __shared__ uint64_t s_cand[32 * kListCap];
     const uint32_t lane = threadIdx.x;
     Walker w{0, 0, cap, ends, false};
+    uint4 na, nb;
+    load_tile_rec(tiles, lane, n_tiles, na, nb);
     for (uint64_t t0 = 0; t0 < n_tiles; t0 += 32) {
-        uint64_t t = t0 + lane;
-        TileRec r;
-        r.count = 0;
-        if (t < n_tiles) {
-            const uint4* q = reinterpret_cast<const uint4*>(tiles + t);
-            uint4 a = __ldg(q);
-            r.count = (uint16_t)(a.x & 0xffff);
-            if (r.count) {
-                uint4 b = __ldg(q + 1);
-                uint32_t ww[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        const uint4 a = na, b = nb;
+        load_tile_rec(tiles, t0 + 32 + lane, n_tiles, na, nb);  // next batch's records are in flight while this one is walked
+        const uint32_t cnt = a.x & 0xffffu;
+        const uint32_t ww[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        const uint64_t tbase = (t0 + lane) * (uint64_t)kTileBytes;
+        const uint32_t dense = __ballot_sync(0xffffffffu, cnt > (uint32_t)kListCap);
+        if (!dense) {
+            // compact the batch's candidates (ascending by construction) into shared memory, then apply the rule
+            uint32_t x = cnt;
 #pragma unroll
-                for (int i = 0; i < kListCap; i++) r.pos[i] = (uint16_t)(ww[(i + 2) >> 1] >> (16 * ((i + 2) & 1)));
+            for (int d = 1; d < 32; d <<= 1) {
+                uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+                if (lane >= (uint32_t)d) x += y;
             }
+            const uint32_t total = __shfl_sync(0xffffffffu, x, 31);
+            uint32_t o = x - cnt;
+#pragma unroll
+            for (int i = 0; i < kListCap; i++)
+                if ((uint32_t)i < cnt) s_cand[o + i] = tbase + ((ww[(i + 2) >> 1] >> (16 * ((i + 2) & 1))) & 0xffffu) + 1;
+            __syncwarp();
+            for (uint32_t j = 0; j < total; j++) w.candidate(s_cand[j], lane);
+            __syncwarp();
+            continue;
         }
-        uint32_t nz = __ballot_sync(0xffffffffu, r.count != 0);
+        // a dense tile in the batch: take the tiles one by one
+        uint32_t nz = __ballot_sync(0xffffffffu, cnt != 0);
         while (nz) {
             int l = __ffs(nz) - 1;
             nz &= nz - 1;
-            uint32_t c = __shfl_sync(0xffffffffu, (uint32_t)r.count, l);
-            uint64_t tbase = (t0 + l) * (uint64_t)kTileBytes;
+            uint32_t c = __shfl_sync(0xffffffffu, cnt, l);
+            uint64_t tb = (t0 + l) * (uint64_t)kTileBytes;
             if (c <= (uint32_t)kListCap) {
 #pragma unroll
                 for (int i = 0; i < kListCap; i++) {
-                    uint32_t p = __shfl_sync(0xffffffffu, (uint32_t)r.pos[i], l);
-                    if ((uint32_t)i < c) w.candidate(tbase + p + 1, lane);
+                    uint32_t p = __shfl_sync(0xffffffffu, (ww[(i + 2) >> 1] >> (16 * ((i + 2) & 1))) & 0xffffu, l);
+                    if ((uint32_t)i < c) w.candidate(tb + p + 1, lane);
                 }
             } else {
                 // dense tile: roll the hash again, but only from where a cut may next fall
-                uint64_t tend = tbase + kTileBytes < len ? tbase + kTileBytes : len;
-                uint64_t p = tbase;
+                uint64_t tend = tb + kTileBytes < len ? tb + kTileBytes : len;
+                uint64_t p = tb;
                 while (p < tend) {
                     while (p + 1 - w.s > kMax) w.emit(w.s + kMax, lane);
                     if (p + 1 - w.s < kMin) p = w.s + kMin - 1;

@@ -15,6 +15,7 @@
 // Roofline: integer-ALU bound.  A block costs 7 x 8 x 12 + 8 = 680 ALU-pipe instructions (IADD3/LOP3/SHF/PRMT);
 // the input is read exactly once (1 B/B of HBM traffic, >= 4x below the HBM roof at ALU speed).
 #include <cstdio>
+#include <cstdlib>
 
 #include "kernels.h"
 
@@ -154,7 +155,7 @@ __device__ __noinline__ void load_block_general(const uint8_t* p, uint32_t blen,
 }
 
 // ---- leaf kernel: one thread = one aligned group of G leaves ------------------------------------------------
-template <int G>
+template <int G, bool FMA_ADDS>
 __global__ void __launch_bounds__(128) hash_leaf_kernel(const uint8_t* __restrict__ data,
                                                         const uint64_t* __restrict__ off,
                                                         const uint32_t* __restrict__ len, const B3Key key,
@@ -197,7 +198,7 @@ __global__ void __launch_bounds__(128) hash_leaf_kernel(const uint8_t* __restric
             else load_block_general(p + 64 * b, blen, m);
             uint32_t fl = key.base_flags | (b == 0 ? B3_CHUNK_START : 0u) |
                           (b == nblk - 1 ? (B3_CHUNK_END | root_leaf) : 0u);
-            b3_compress(cv, m, leaf, 0, blen, fl);
+            b3_compress<FMA_ADDS>(cv, m, leaf, 0, blen, fl, key.one);
         }
         if (G == 1) break;
         // push, then merge completed sub-trees: after leaf l (count l+1), one merge per trailing zero bit; after
@@ -238,71 +239,40 @@ __device__ __forceinline__ void store_cv(uint4* p, const uint32_t (&cv)[8]) {
     p[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
 }
 
-constexpr uint32_t kSerialMax = 16;  // chunks with up to this many nodes are folded by a single thread
-
+// A team of T lanes (T = 1..32, power of two) folds one chunk's group nodes level by level, in place in the node
+// array: pairs are combined left to right, an odd tail is promoted unchanged (== BLAKE3's left-full tree,
+// SURVEY.md A.2), ROOT goes on the last parent.  Teams are packed side by side in a warp, so lanes stay busy across
+// chunks; any node count works (a 16 MiB chunk just loops).
 __global__ void __launch_bounds__(128) hash_tree_kernel(const B3Key key, const uint32_t* __restrict__ P, size_t n,
-                                                        uint4* __restrict__ nodes, uint4* __restrict__ out) {
-    uint32_t lane = threadIdx.x & 31;
-    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    size_t ci = warp * 32 + lane;
-    uint32_t base = 0, m = 0;
-    if (ci < n) { base = P[ci]; m = P[ci + 1] - base; }
-
-    if (m >= 2 && m <= kSerialMax) {
-        // incremental left-full tree: push node j, merge once per trailing zero of (j+1); then right-to-left
-        uint32_t stack[5][8];
-        int sp = 0;
-        uint32_t cv[8];
-        for (uint32_t j = 0; j < m; j++) {
-            load_cv(nodes + 2 * (size_t)(base + j), cv);
-            bool last = (j == m - 1);
-            uint32_t cnt = j + 1;
-            while (sp > 0 && (last || (cnt & 1) == 0)) {
-                uint32_t left[8], r[8];
-#pragma unroll
-                for (int i = 0; i < 8; i++) { left[i] = stack[sp - 1][i]; r[i] = cv[i]; }
-                sp--;
-                b3_parent(cv, key.w, left, r, key.base_flags | B3_PARENT | ((last && sp == 0) ? B3_ROOT : 0u));
-                cnt >>= 1;
+                                                        uint32_t team, uint4* __restrict__ nodes,
+                                                        uint4* __restrict__ out) {
+    const uint32_t lane = threadIdx.x & 31;
+    const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t ci = gt / team;
+    const uint32_t lt = (uint32_t)(gt % team);
+    const uint32_t tmask = (team == 32 ? 0xffffffffu : ((1u << team) - 1u)) << (lane & ~(team - 1));
+    uint32_t base = 0, cnt = 0;
+    if (ci < n) { base = P[ci]; cnt = P[ci + 1] - base; }
+    uint4* nd = nodes + 2 * (size_t)base;
+    while (cnt > 1) {
+        const uint32_t pairs = cnt >> 1;
+        const bool root = (cnt == 2);
+        for (uint32_t p0 = 0; p0 < pairs; p0 += team) {
+            const uint32_t p = p0 + lt;
+            uint32_t l[8], r[8], o[8];
+            if (p < pairs) { load_cv(nd + 2 * (size_t)(2 * p), l); load_cv(nd + 2 * (size_t)(2 * p + 1), r); }
+            __syncwarp(tmask);
+            if (p < pairs) {
+                b3_parent(o, key.w, l, r, key.base_flags | B3_PARENT | (root ? B3_ROOT : 0u));
+                store_cv(root ? out + 2 * ci : nd + 2 * (size_t)p, o);
             }
-            if (!last) {
-#pragma unroll
-                for (int i = 0; i < 8; i++) stack[sp][i] = cv[i];
-                sp++;
-            }
+            __syncwarp(tmask);
         }
-        store_cv(out + 2 * ci, cv);
-    }
-
-    // very large chunks: the whole warp folds one chunk level by level, in place in the node array
-    uint32_t big = __ballot_sync(0xffffffffu, m > kSerialMax);
-    while (big) {
-        int src = __ffs(big) - 1;
-        big &= big - 1;
-        uint32_t b0 = __shfl_sync(0xffffffffu, base, src), cnt = __shfl_sync(0xffffffffu, m, src);
-        size_t cj = warp * 32 + src;
-        uint4* nd = nodes + 2 * (size_t)b0;
-        while (cnt > 1) {
-            uint32_t pairs = cnt >> 1;
-            for (uint32_t p0 = 0; p0 < pairs; p0 += 32) {
-                uint32_t p = p0 + lane;
-                uint32_t l[8], r[8], o[8];
-                if (p < pairs) { load_cv(nd + 2 * (size_t)(2 * p), l); load_cv(nd + 2 * (size_t)(2 * p + 1), r); }
-                __syncwarp();
-                if (p < pairs) {
-                    b3_parent(o, key.w, l, r, key.base_flags | B3_PARENT | (cnt == 2 ? B3_ROOT : 0u));
-                    store_cv(nd + 2 * (size_t)p, o);
-                }
-                __syncwarp();
-            }
-            if (cnt & 1) {
-                if (lane == 0) { uint32_t t[8]; load_cv(nd + 2 * (size_t)(cnt - 1), t); store_cv(nd + 2 * (size_t)pairs, t); }
-                __syncwarp();
-            }
-            cnt = pairs + (cnt & 1);
+        if (cnt & 1) {
+            if (lt == 0) { uint32_t t[8]; load_cv(nd + 2 * (size_t)(cnt - 1), t); store_cv(nd + 2 * (size_t)pairs, t); }
+            __syncwarp(tmask);
         }
-        if (lane == 0) { uint32_t t[8]; load_cv(nd, t); store_cv(out + 2 * cj, t); }
-        __syncwarp();
+        cnt = pairs + (cnt & 1);
     }
 }
 
@@ -326,8 +296,8 @@ HashLayout hash_layout(uint64_t data_bytes, size_t n, int group) {
 }  // namespace
 
 int hash_pick_group(uint64_t data_bytes) {
-    // keep >= ~96K threads (148 SMs x ~20 warps) busy; beyond that fold more leaves per thread
-    const uint64_t want = 148ull * 32 * 20;
+    // keep >= ~57K threads (148 SMs x 12 warps) busy; beyond that fold more leaves per thread
+    const uint64_t want = 148ull * 32 * 12;
     for (int g = 8; g > 1; g >>= 1)
         if (data_bytes / ((uint64_t)kLeaf * g) >= want) return g;
     return 1;
@@ -353,13 +323,23 @@ cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const u
     hash_map_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(off, len, n, gb, P, tiles, map);
     unsigned blocks = (unsigned)((L.slots_cap + 127) / 128);
     uint4* o4 = reinterpret_cast<uint4*>(out);
+    static const bool fma_adds = []() { const char* e = getenv("ZEST_B3_PLAIN_ADDS"); return !(e && e[0] == '1'); }();
+#define ZG_LEAF(G)                                                                                                    \
+    do {                                                                                                              \
+        if (fma_adds) hash_leaf_kernel<G, true><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); \
+        else hash_leaf_kernel<G, false><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4);        \
+    } while (0)
     switch (group) {
-        case 1: hash_leaf_kernel<1><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); break;
-        case 2: hash_leaf_kernel<2><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); break;
-        case 4: hash_leaf_kernel<4><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); break;
-        default: hash_leaf_kernel<8><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); break;
+        case 1: ZG_LEAF(1); break;
+        case 2: ZG_LEAF(2); break;
+        case 4: ZG_LEAF(4); break;
+        default: ZG_LEAF(8); break;
     }
-    hash_tree_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(key, P, n, nodes, o4);
+#undef ZG_LEAF
+    // team size: a 128 KiB chunk has 128 / G nodes; give each chunk a quarter of that in lanes
+    uint32_t team = group == 8 ? 4u : (group == 4 ? 8u : (group == 2 ? 16u : 32u));
+    size_t tthreads = n * team;
+    hash_tree_kernel<<<(unsigned)((tthreads + 127) / 128), 128, 0, st>>>(key, P, n, team, nodes, o4);
     return cudaGetLastError();
 }
 

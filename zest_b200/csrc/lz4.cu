@@ -22,6 +22,8 @@
 //
 // Roofline: HBM-bound in principle (compressed bytes in + decoded bytes out); in practice bounded by issue slots
 // and L1 wavefronts per sequence.  bench.py reports achieved GB/s over those algorithmic bytes.
+#include <cstdlib>
+
 #include "kernels.h"
 
 namespace zg {
@@ -29,9 +31,8 @@ namespace zg {
 namespace {
 
 constexpr int kWarps = 4;          // warps per CTA
-constexpr int kSeqCap = 16;        // records parsed per slot per round
-constexpr uint32_t kShortLit = 16; // literal runs up to this length are copied by their own lane
-constexpr uint32_t kShortMatch = 16;
+constexpr int kSeqCap = 16;        // records parsed per slot per round (two slots share one 32-lane execute step)
+constexpr uint32_t kShort = 16;    // literal runs / matches up to this length are copied by their own lane
 constexpr uint32_t kMaxPiece = 65535;
 
 enum : int { ST_IDLE = 0, ST_START, ST_BLOCK_HDR, ST_IN_BLOCK, ST_AFTER_BLOCK, ST_FINISH, ST_EXHAUSTED };
@@ -41,6 +42,16 @@ struct Seq {           // 16 bytes
     uint32_t dst;      // destination of the literals, relative to the chunk's LZ4 output
     uint32_t lens;     // literal length | match length << 16
     uint32_t off;      // match offset (1..65535)
+};
+
+struct WarpShared {
+    Seq rec[kSeqCap * 32];         // record s of slot c lives at [s * 32 + (c ^ s)] (conflict-free both ways)
+    unsigned long long src[32];    // per slot: payload base
+    unsigned long long lz[32];     // per slot: LZ4 output base
+    uint32_t pend[32];             // per slot: records whose match is still to be copied (bit s)
+    uint32_t frontier[32];         // per slot: output offset below which everything is final this round
+    uint8_t first[32];             // per slot: index of the first pending match
+    uint8_t cnt[32];               // per slot: records parsed this round
 };
 
 __device__ __forceinline__ uint32_t rd8(const uint8_t* p) { return __ldg(p); }
@@ -57,6 +68,38 @@ __device__ uint32_t xxh32_small(const uint8_t* p, uint32_t len) {
     for (; i < len; i++) h = rotl32(h + rd8(p + i) * P5, 11) * P1;
     h ^= h >> 15; h *= P2; h ^= h >> 13; h *= P3; h ^= h >> 16;
     return h;
+}
+
+// Eight stream bytes at any alignment as one u64 (three aligned word loads, issued together).  May touch the
+// aligned words just past p + 7; the compressed buffer is padded by 16 bytes for that.
+__device__ __forceinline__ uint64_t load_window(const uint8_t* p) {
+    uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+    uint32_t sh = (uint32_t)(a & 3) * 8;
+    uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    return (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
+}
+
+// Up to 16 bytes from any alignment into four words: all loads are issued before anything is stored, so a lane
+// pays one memory latency per copy instead of one per byte.  Only aligned words holding wanted bytes are read.
+template <bool READ_ONLY>
+__device__ __forceinline__ void load16(const uint8_t* s, uint32_t n, uint32_t (&x)[4]) {
+    uintptr_t a = reinterpret_cast<uintptr_t>(s);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+    uint32_t sh = (uint32_t)(a & 3) * 8, span = n ? (uint32_t)(a & 3) + n : 0;
+    uint32_t v[5];
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        v[k] = 0;
+        if (span > 4u * k) v[k] = READ_ONLY ? __ldg(w + k) : w[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) x[k] = __funnelshift_r(v[k], v[k + 1], sh);
+}
+__device__ __forceinline__ void store16(uint8_t* d, uint32_t n, const uint32_t (&x)[4]) {
+#pragma unroll
+    for (int i = 0; i < 16; i++)
+        if ((uint32_t)i < n) d[i] = (uint8_t)(x[i >> 2] >> (8 * (i & 3)));
 }
 
 // Whole-warp copy of non-overlapping ranges, any alignment.  Destination words are written aligned; the source
@@ -95,8 +138,7 @@ __device__ __forceinline__ void warp_match(uint8_t* dst, uint32_t off, uint32_t 
         warp_copy<true>(dst, src, n, lane);
         __syncwarp();
         dst += n; len -= n;
-        avail += n - (n % off);  // keep the distance a multiple of the period
-        if (n % off) break;       // only the final piece can be a partial period
+        avail += n;  // n is a whole number of periods except for the final piece
     }
 }
 
@@ -124,11 +166,9 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                                                                  const ChunkDesc* __restrict__ chunks, uint32_t n_chunks,
                                                                  uint8_t* out, uint8_t* tmp, int32_t* __restrict__ status,
                                                                  uint32_t* ticket, uint32_t slots) {
-    __shared__ Seq s_list[kWarps][kSeqCap * 32];
-    __shared__ uint8_t s_cnt[kWarps][32];
+    __shared__ __align__(16) WarpShared s_ws[kWarps];
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    Seq* list = s_list[wid];
-    uint8_t* cnts = s_cnt[wid];
+    WarpShared& ws = s_ws[wid];
 
     // per-slot (per-lane) parser state
     int state = lane < slots ? ST_IDLE : ST_EXHAUSTED;
@@ -156,6 +196,8 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                     src = comp + d.src_off;
                     fin_out = out + d.dst_off;
                     lz = scheme == 2 ? tmp + d.dst_off : fin_out;
+                    ws.src[lane] = reinterpret_cast<unsigned long long>(src);
+                    ws.lz[lane] = reinterpret_cast<unsigned long long>(lz);
                     ip = 0; op = 0; err = 0; p_lit = p_mlen = 0;
                     state = ST_START;
                 } else
@@ -165,14 +207,77 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
         if (__all_sync(0xffffffffu, state == ST_EXHAUSTED)) break;
 
         // ---- parse: every active lane appends up to kSeqCap records for its own chunk
-        uint32_t cnt = 0;
+        uint32_t cnt = 0, pmask = 0;
         bool finished = false;  // chunk complete (ok or error) after this round's records
+        // Control flow matters here: lanes run in lock-step only while they take the same path, so the common case
+        // (one LZ4 sequence -> one record) is a single straight-line iteration; block/frame boundaries, oversized
+        // pieces and errors leave it for the state machine below and rejoin on the next iteration.
         while (cnt < (uint32_t)kSeqCap && state != ST_IDLE && state != ST_EXHAUSTED && !finished) {
+            if (state == ST_IN_BLOCK && (p_lit | p_mlen) == 0) {
+                // One sequence.  The checks and their order are those of the oracle's lz4_block; the bytes come from
+                // an 8-byte window fetched with one round trip (token, short literal run and offset usually all sit
+                // inside it).
+                if (ip >= bend) { err = E_LZ4_BLOCK; finished = true; continue; }
+                const uint32_t ip0 = ip;
+                const uint64_t win = load_window(src + ip0);
+                const uint32_t tok = (uint32_t)win & 0xffu;
+                ip++;
+                uint32_t lit = tok >> 4;
+                bool bad = false;
+                if (lit == 15) {
+                    uint32_t b;
+                    do {
+                        if (ip >= bend) { bad = true; break; }
+                        b = rd8(src + ip++);
+                        lit += b;
+                    } while (b == 255);
+                }
+                if (bad || lit > bend - ip) { err = E_LZ4_BLOCK; finished = true; continue; }
+                if (lit > ulen - op) { err = E_SIZE_MISMATCH; finished = true; continue; }
+                const uint32_t lsrc = ip;
+                ip += lit;
+                if (ip == bend) {  // last sequence of the block: literals only
+                    p_lit = lit; p_lsrc = lsrc;
+                    state = ST_AFTER_BLOCK;
+                    continue;
+                }
+                if (bend - ip < 2) { err = E_LZ4_BLOCK; finished = true; continue; }
+                const uint32_t rel = ip - ip0;
+                uint32_t off;
+                if (rel <= 6) off = (uint32_t)(win >> (8 * rel)) & 0xffffu;
+                else off = rd8(src + ip) | (rd8(src + ip + 1) << 8);
+                ip += 2;
+                uint32_t ml = tok & 15;
+                if (ml == 15) {
+                    uint32_t b;
+                    do {
+                        if (ip >= bend) { bad = true; break; }
+                        b = rd8(src + ip++);
+                        ml += b;
+                    } while (b == 255);
+                }
+                if (bad) { err = E_LZ4_BLOCK; finished = true; continue; }
+                ml += 4;
+                const uint32_t vop = op + lit;
+                if (off == 0 || off > vop - win_lo) { err = E_LZ4_BLOCK; finished = true; continue; }
+                if (ml > ulen - vop) { err = E_SIZE_MISMATCH; finished = true; continue; }
+                if (lit <= kMaxPiece && ml <= kMaxPiece) {
+                    Seq e{lsrc, op, lit | (ml << 16), off};
+                    ws.rec[cnt * 32 + (lane ^ cnt)] = e;
+                    pmask |= 1u << cnt;
+                    cnt++;
+                    op = vop + ml;
+                } else {
+                    p_lit = lit; p_lsrc = lsrc; p_mlen = ml; p_off = off;  // split into pieces below
+                }
+                continue;
+            }
             if (p_lit | p_mlen) {
                 uint32_t l = p_lit < kMaxPiece ? p_lit : kMaxPiece;
                 uint32_t m = (l == p_lit) ? (p_mlen < kMaxPiece ? p_mlen : kMaxPiece) : 0u;
                 Seq e{p_lsrc, op, l | (m << 16), p_off};
-                list[cnt * 32 + (lane ^ cnt)] = e;
+                ws.rec[cnt * 32 + (lane ^ cnt)] = e;
+                if (m) pmask |= 1u << cnt;
                 cnt++;
                 op += l + m; p_lsrc += l; p_lit -= l; p_mlen -= m;
                 continue;
@@ -231,48 +336,6 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                     }
                     break;
                 }
-                case ST_IN_BLOCK: {
-                    if (ip >= bend) { err = E_LZ4_BLOCK; finished = true; break; }
-                    uint32_t tok = rd8(src + ip++);
-                    uint32_t lit = tok >> 4;
-                    bool bad = false;
-                    if (lit == 15) {
-                        uint32_t b;
-                        do {
-                            if (ip >= bend) { bad = true; break; }
-                            b = rd8(src + ip++);
-                            lit += b;
-                        } while (b == 255);
-                    }
-                    if (bad || lit > bend - ip) { err = E_LZ4_BLOCK; finished = true; break; }
-                    if (lit > ulen - op) { err = E_SIZE_MISMATCH; finished = true; break; }
-                    uint32_t lsrc = ip;
-                    ip += lit;
-                    if (ip == bend) {  // last sequence of the block: literals only
-                        p_lit = lit; p_lsrc = lsrc;
-                        state = ST_AFTER_BLOCK;
-                        break;
-                    }
-                    if (bend - ip < 2) { err = E_LZ4_BLOCK; finished = true; break; }
-                    uint32_t off = rd8(src + ip) | (rd8(src + ip + 1) << 8);
-                    ip += 2;
-                    uint32_t ml = tok & 15;
-                    if (ml == 15) {
-                        uint32_t b;
-                        do {
-                            if (ip >= bend) { bad = true; break; }
-                            b = rd8(src + ip++);
-                            ml += b;
-                        } while (b == 255);
-                    }
-                    if (bad) { err = E_LZ4_BLOCK; finished = true; break; }
-                    ml += 4;
-                    uint32_t vop = op + lit;
-                    if (off == 0 || off > vop - win_lo) { err = E_LZ4_BLOCK; finished = true; break; }
-                    if (ml > ulen - vop) { err = E_SIZE_MISMATCH; finished = true; break; }
-                    p_lit = lit; p_lsrc = lsrc; p_mlen = ml; p_off = off;
-                    break;
-                }
                 case ST_AFTER_BLOCK: {  // pending literals of the block have been emitted: op is the block end
                     if (op - blk_op > bmax && blk_op <= op) { err = E_LZ4_FRAME; finished = true; break; }
                     if (fflags & 2) {
@@ -286,75 +349,121 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                 default: finished = true; break;
             }
         }
-        cnts[lane] = (uint8_t)cnt;
+        ws.cnt[lane] = (uint8_t)cnt;
+        ws.pend[lane] = pmask;
+        __syncwarp();
+        const uint32_t have = __ballot_sync(0xffffffffu, cnt > 0);  // slots with records this round
+
+        // ---- execute, pass L: every literal run of every slot (independent of each other).  A 32-lane step covers
+        // two slots x 16 records; two steps are issued back to back so four slots' loads are in flight at once.
+        const uint32_t half = lane >> 4, s = lane & 15;
+#pragma unroll 1
+        for (uint32_t it = 0; it < 16; it += 2) {
+            if (((have >> (2 * it)) & 0xfu) == 0) continue;
+            const uint32_t cA = 2 * it + half, cB = cA + 2;
+            Seq eA{0, 0, 0, 0}, eB{0, 0, 0, 0};
+            if (s < ws.cnt[cA]) eA = ws.rec[s * 32 + (cA ^ s)];
+            if (s < ws.cnt[cB]) eB = ws.rec[s * 32 + (cB ^ s)];
+            const uint32_t litA = eA.lens & 0xffffu, litB = eB.lens & 0xffffu;
+            const uint8_t* sA = reinterpret_cast<const uint8_t*>(ws.src[cA]) + eA.lit_src;
+            const uint8_t* sB = reinterpret_cast<const uint8_t*>(ws.src[cB]) + eB.lit_src;
+            uint8_t* dA = reinterpret_cast<uint8_t*>(ws.lz[cA]) + eA.dst;
+            uint8_t* dB = reinterpret_cast<uint8_t*>(ws.lz[cB]) + eB.dst;
+            uint32_t xA[4], xB[4];
+            const uint32_t nA = litA <= kShort ? litA : 0u, nB = litB <= kShort ? litB : 0u;
+            load16<true>(sA, nA, xA);
+            load16<true>(sB, nB, xB);
+            store16(dA, nA, xA);
+            store16(dB, nB, xB);
+            uint32_t lA = __ballot_sync(0xffffffffu, litA > kShort), lB = __ballot_sync(0xffffffffu, litB > kShort);
+            while (lA) {
+                int l = __ffs(lA) - 1;
+                lA &= lA - 1;
+                uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dA), l));
+                const uint8_t* q = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(sA), l));
+                warp_copy<false>(d, q, __shfl_sync(0xffffffffu, litA, l), lane);
+            }
+            while (lB) {
+                int l = __ffs(lB) - 1;
+                lB &= lB - 1;
+                uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dB), l));
+                const uint8_t* q = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(sB), l));
+                warp_copy<false>(d, q, __shfl_sync(0xffffffffu, litB, l), lane);
+            }
+        }
         __syncwarp();
 
-        // ---- execute: one slot at a time, one record per lane
-        uint32_t active = __ballot_sync(0xffffffffu, cnt > 0 || finished);
-        while (active) {
-            int c = __ffs(active) - 1;
-            active &= active - 1;
-            uint32_t n_rec = cnts[c];
-            const uint8_t* c_src = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(src), c));
-            uint8_t* c_lz = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(lz), c));
-            Seq e{0, 0, 0, 0};
-            if (lane < n_rec) e = list[lane * 32 + ((uint32_t)c ^ lane)];
-            uint32_t lit = e.lens & 0xffffu, ml = e.lens >> 16;
-            uint8_t* d = c_lz + e.dst;
-            // literals
-            if (lit && lit <= kShortLit) {
-                const uint8_t* s = c_src + e.lit_src;
-                for (uint32_t b = 0; b < lit; b++) d[b] = __ldg(s + b);
+        // ---- execute, pass M: matches.  Per slot they are ordered; a match may run as soon as its source lies below
+        // the slot's frontier (start of the first match still pending), so every round retires at least one match per
+        // slot and usually most of them.
+        for (;;) {
+            uint32_t p = ws.pend[lane];
+            if (p) {
+                uint32_t f = (uint32_t)__ffs(p) - 1;
+                Seq e = ws.rec[f * 32 + (lane ^ f)];
+                ws.first[lane] = (uint8_t)f;
+                ws.frontier[lane] = e.dst + (e.lens & 0xffffu);
             }
-            uint32_t longlit = __ballot_sync(0xffffffffu, lit > kShortLit);
-            while (longlit) {
-                int l = __ffs(longlit) - 1;
-                longlit &= longlit - 1;
-                uint32_t l_src = __shfl_sync(0xffffffffu, e.lit_src, l), l_dst = __shfl_sync(0xffffffffu, e.dst, l),
-                         l_len = __shfl_sync(0xffffffffu, lit, l);
-                warp_copy<false>(c_lz + l_dst, c_src + l_src, l_len, lane);
-            }
+            const uint32_t anyp = __ballot_sync(0xffffffffu, p != 0);
+            if (!anyp) break;
             __syncwarp();
-            // matches, in order where they depend on each other
-            uint8_t* md = d + lit;
-            uint32_t m_dst = e.dst + lit;                 // relative start of this lane's match output
-            uint32_t m_src_end = m_dst - e.off + ml;      // relative end of its source range
-            uint32_t pending = __ballot_sync(0xffffffffu, ml > 0);
-            while (pending) {
-                int f = __ffs(pending) - 1;
-                uint32_t f_ml = __shfl_sync(0xffffffffu, ml, f);
-                if (f_ml > kShortMatch) {
-                    uint32_t f_dst = __shfl_sync(0xffffffffu, m_dst, f), f_off = __shfl_sync(0xffffffffu, e.off, f);
-                    warp_match(c_lz + f_dst, f_off, f_ml, lane);
-                    pending &= pending - 1;
-                    __syncwarp();
-                    continue;
+#pragma unroll 1
+            for (uint32_t it = 0; it < 16; it += 2) {
+                if (((anyp >> (2 * it)) & 0xfu) == 0) continue;
+                const uint32_t cA = 2 * it + half, cB = cA + 2;
+                Seq eA{0, 0, 0, 0}, eB{0, 0, 0, 0};
+                const bool pA = (ws.pend[cA] >> s) & 1, pB = (ws.pend[cB] >> s) & 1;
+                if (pA) eA = ws.rec[s * 32 + (cA ^ s)];
+                if (pB) eB = ws.rec[s * 32 + (cB ^ s)];
+                const uint32_t mlA = eA.lens >> 16, mlB = eB.lens >> 16;
+                const uint32_t mdA = eA.dst + (eA.lens & 0xffffu), mdB = eB.dst + (eB.lens & 0xffffu);
+                const bool fA = pA && s == ws.first[cA], fB = pB && s == ws.first[cB];
+                uint8_t* dA = reinterpret_cast<uint8_t*>(ws.lz[cA]) + mdA;
+                uint8_t* dB = reinterpret_cast<uint8_t*>(ws.lz[cB]) + mdB;
+                // long matches run when they are first in their slot, with the whole warp
+                uint32_t longA = __ballot_sync(0xffffffffu, fA && mlA > kShort), longB = __ballot_sync(0xffffffffu, fB && mlB > kShort);
+                while (longA) {
+                    int l = __ffs(longA) - 1;
+                    longA &= longA - 1;
+                    uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dA), l));
+                    warp_match(d, __shfl_sync(0xffffffffu, eA.off, l), __shfl_sync(0xffffffffu, mlA, l), lane);
                 }
-                uint32_t frontier = __shfl_sync(0xffffffffu, m_dst, f);
-                bool go = ((pending >> lane) & 1) && ml <= kShortMatch && ((int)lane == f || m_src_end <= frontier);
-                if (go) {
-                    const uint8_t* ms = md - e.off;
-                    for (uint32_t b = 0; b < ml; b++) md[b] = ms[b];
+                while (longB) {
+                    int l = __ffs(longB) - 1;
+                    longB &= longB - 1;
+                    uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dB), l));
+                    warp_match(d, __shfl_sync(0xffffffffu, eB.off, l), __shfl_sync(0xffffffffu, mlB, l), lane);
                 }
-                __syncwarp();
-                pending &= ~__ballot_sync(0xffffffffu, go);
-            }
-            // chunk finished in this round: regroup (scheme 2) and publish its status
-            uint32_t c_done = __shfl_sync(0xffffffffu, (uint32_t)finished, c);
-            if (c_done) {
-                int c_err = __shfl_sync(0xffffffffu, err, c);
-                uint32_t c_scheme = __shfl_sync(0xffffffffu, scheme, c);
-                if (c_err == 0 && c_scheme == 2) {
-                    uint8_t* c_out = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(fin_out), c));
-                    uint32_t c_ulen = __shfl_sync(0xffffffffu, ulen, c);
-                    warp_regroup(c_out, c_lz, c_ulen, lane);
-                }
+                const bool goA = pA && mlA <= kShort && (fA || mdA - eA.off + mlA <= ws.frontier[cA]);
+                const bool goB = pB && mlB <= kShort && (fB || mdB - eB.off + mlB <= ws.frontier[cB]);
+                const bool fastA = goA && eA.off >= mlA, fastB = goB && eB.off >= mlB;
+                uint32_t xA[4], xB[4];
+                load16<false>(dA - eA.off, fastA ? mlA : 0u, xA);
+                load16<false>(dB - eB.off, fastB ? mlB : 0u, xB);
+                store16(dA, fastA ? mlA : 0u, xA);
+                store16(dB, fastB ? mlB : 0u, xB);
+                if (goA && !fastA) { const uint8_t* q = dA - eA.off; for (uint32_t b = 0; b < mlA; b++) dA[b] = q[b]; }
+                if (goB && !fastB) { const uint8_t* q = dB - eB.off; for (uint32_t b = 0; b < mlB; b++) dB[b] = q[b]; }
+                if (goA || (fA && mlA > kShort)) atomicAnd(&ws.pend[cA], ~(1u << s));
+                if (goB || (fB && mlB > kShort)) atomicAnd(&ws.pend[cB], ~(1u << s));
             }
             __syncwarp();
         }
+
+        // ---- chunks that finished this round: regroup (scheme 2) and publish the status
+        uint32_t fin = __ballot_sync(0xffffffffu, finished);
+        while (fin) {
+            int c = __ffs(fin) - 1;
+            fin &= fin - 1;
+            int c_err = __shfl_sync(0xffffffffu, err, c);
+            uint32_t c_scheme = __shfl_sync(0xffffffffu, scheme, c);
+            if (c_err == 0 && c_scheme == 2) {
+                uint8_t* c_out = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(fin_out), c));
+                const uint8_t* c_lz = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(lz), c));
+                warp_regroup(c_out, c_lz, __shfl_sync(0xffffffffu, ulen, c), lane);
+            }
+        }
         if (finished) {
-            if (state != ST_FINISH || err) { /* LZ4 chunks validated op == ulen at the EndMark */ }
-            else if (op != ulen) err = E_SIZE_MISMATCH;
             status[ci] = err;
             state = ST_IDLE;
         }
@@ -379,13 +488,16 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     uint8_t* tmp = sb + 256;
     cudaError_t e = cudaMemsetAsync(ticket, 0, 256, st);
     if (e != cudaSuccess) return e;
-    // slots per warp: enough warps to give every SM several, at most 32 chunks per warp
-    size_t want_warps = 148 * 8;
+    // Slots (chunks in flight) per warp: few when the batch is small, so that every SM gets several warps; up to 32
+    // for large batches, where the serial token walk is then spread over all lanes.  ZEST_LZ4_SLOTS /
+    // ZEST_LZ4_WARPS override the heuristic (tuning knobs).
+    size_t want_warps = 148 * 12, max_warps = 148 * 16;
+    if (const char* e = getenv("ZEST_LZ4_WARPS")) { long v = atol(e); if (v > 0) want_warps = max_warps = (size_t)v; }
     uint32_t slots = (uint32_t)((n + want_warps - 1) / want_warps);
+    if (const char* e = getenv("ZEST_LZ4_SLOTS")) { long v = atol(e); if (v > 0) slots = (uint32_t)v; }
     if (slots < 1) slots = 1;
     if (slots > 32) slots = 32;
     size_t warps = (n + slots - 1) / slots;
-    size_t max_warps = 148 * 16;
     if (warps > max_warps) warps = max_warps;
     unsigned blocks = (unsigned)((warps + kWarps - 1) / kWarps);
     lz4_decode_kernel<<<blocks, kWarps * 32, 0, st>>>(comp, chunks, (uint32_t)n, out, tmp, status, ticket, slots);

@@ -68,7 +68,7 @@ __device__ uint64_t hash_group(const NodeView& in, size_t first, int cnt, const 
         for (int i = 0; i < 16; i++) m[i] = buf32[16 * b + i];
         uint32_t blen = pos - 64 * b < 64 ? pos - 64 * b : 64;
         uint32_t fl = B3_KEYED | (b == 0 ? B3_CHUNK_START : 0u) | (b == nblk - 1 ? (B3_CHUNK_END | B3_ROOT) : 0u);
-        b3_compress(cv, m, 0, 0, blen, fl);
+        b3_compress<false>(cv, m, 0, 0, blen, fl);
     }
     uint32_t* o = reinterpret_cast<uint32_t*>(out_h);
 #pragma unroll
