@@ -206,6 +206,7 @@ def main():
             k += 1
         cpos += (len(b) + 15) // 16 * 16
     first[nx] = k
+    L.zg_chunk_order(C.byref(descs), nchunks)
     out_bytes = dpos
     d_comp = torch.from_numpy(comp_host[:cpos + 16]).to(dev)
     d_desc = torch.from_numpy(np.frombuffer(descs, np.uint8).copy()).to(dev)

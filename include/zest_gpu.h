@@ -141,8 +141,14 @@ ZG_API int zg_cdc_hash(zg_ctx* ctx, const uint8_t* data, size_t len, uint64_t* e
 typedef struct zg_chunk_desc { /* one per chunk; fill from zg_xorb_index (src_off = hdr_off + 8 + blob base) */
     uint64_t src_off;          /* payload offset inside the compressed buffer                       */
     uint64_t dst_off;          /* where the decoded chunk goes inside the output buffer             */
-    uint32_t clen, ulen, scheme, pad;
+    uint32_t clen, ulen, scheme;
+    uint32_t order;            /* work order, filled by zg_chunk_order: the t-th chunk decoded is descs[t].order */
 } zg_chunk_desc;
+
+/* Fill descs[t].order (host memory) with a longest-first permutation of 0..n-1.  Must be called before the
+ * descriptors are copied to the device: the decoder hands chunks out in this order so that its last warps do not
+ * finish alone.  No counterpart in zest (scheduling detail of the GPU decoder). */
+ZG_API void zg_chunk_order(zg_chunk_desc* descs, size_t n);
 
 ZG_API size_t zg_dev_hash_scratch_bytes(uint64_t data_bytes, size_t n);
 ZG_API int zg_dev_hash_chunks(zg_ctx* ctx, const uint8_t* d_data, uint64_t data_bytes, const uint64_t* d_offsets,

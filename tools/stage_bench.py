@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--sweep", default="")
     ap.add_argument("--warps", default="")
+    ap.add_argument("--oversub", default="")
     ap.add_argument("--cdc", action="store_true")
     args = ap.parse_args()
     nbytes = args.bytes or bench.WORKLOADS[args.workload]["nbytes"]
@@ -53,6 +54,7 @@ def main():
             k += 1
         cpos += (len(b) + 15) // 16 * 16
     first[nx] = k
+    L.zg_chunk_order(C.byref(descs), nchunks)
     out_bytes = dpos
     comp_bytes = sum(len(b) for b in blobs)
     d_comp = torch.from_numpy(comp).to(dev)
@@ -105,7 +107,11 @@ def main():
     res = {}
     sweeps = [s for s in args.sweep.split(",") if s] or [""]
     warps = [w for w in args.warps.split(",") if w] or [""]
-    for w in warps:
+    overs = [o for o in args.oversub.split(",") if o] or [""]
+    for w in [(a, b) for a in warps for b in overs]:
+        w, ov = w
+        if ov:
+            os.environ["ZEST_LZ4_OVERSUB"] = ov
         for s in sweeps:
             os.environ.pop("ZEST_LZ4_SLOTS", None); os.environ.pop("ZEST_LZ4_WARPS", None)
             if s:
@@ -115,7 +121,12 @@ def main():
             d_out.zero_()
             ok = check_all()
             ms = timed(k_decode, args.steps)
-            print(f"decode slots={s or 'auto':>4} warps={w or 'auto':>5}: {ms:8.3f} ms  {total/ms/1e6:8.1f} GB/s uncompressed  {(total+comp_bytes)/ms/1e6:8.1f} GB/s alg  parity={'ok' if ok else 'FAIL'}", flush=True)
+            if os.environ.get("ZG_PROF"):
+                k_decode(); torch.cuda.synchronize()
+                pr = s_dec[16:64].cpu().numpy().view(np.uint64)
+                tot = float(pr[:4].sum()) or 1.0
+                print(f"      phase cycles: parse {pr[0]/tot:.3f} pass1 {pr[1]/tot:.3f} pass2 {pr[2]/tot:.3f} fin {pr[3]/tot:.3f}  rounds/warp-sum {pr[4]} p2-rounds {pr[5]}  total warp-cycles {tot:.3e}")
+            print(f"decode slots={s or 'auto':>4} warps={w or 'auto':>5} oversub={ov or 'auto':>2}: {ms:8.3f} ms  {total/ms/1e6:8.1f} GB/s uncompressed  {(total+comp_bytes)/ms/1e6:8.1f} GB/s alg  parity={'ok' if ok else 'FAIL'}", flush=True)
             res[f"decode_s{s}_w{w}"] = ms
     os.environ.pop("ZEST_LZ4_SLOTS", None); os.environ.pop("ZEST_LZ4_WARPS", None)
     ms = timed(k_hash, args.steps)

@@ -347,6 +347,7 @@ int zg_extract_chunk_range(zg_ctx* ctx, const uint8_t* blob, size_t len, uint32_
         hd[i] = ChunkDesc{ix.hdr_off[k] + 8 - src0, dpos, ix.clen[k], ix.ulen[k], ix.scheme[k], 0};
         dpos += ix.ulen[k];
     }
+    fill_decode_order(hd, cnt);
     ChunkDesc* dd = static_cast<ChunkDesc*>(L.meta.p);
     int32_t* dstatus = reinterpret_cast<int32_t*>(static_cast<uint8_t*>(L.meta.p) + align_up(cnt * sizeof(ChunkDesc), 256));
     CU(cudaMemcpyAsync(L.comp.p, blob + src0, cbytes, cudaMemcpyHostToDevice, L.st));
@@ -486,6 +487,7 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
             if (expected) memcpy(hexp + 32 * i, expected + 32 * (x0 + i), 32);
         }
         hfirst[nx] = (uint32_t)k;
+        fill_decode_order(hd, k);
         uint8_t* dm = static_cast<uint8_t*>(L.meta.p);
         uint8_t* dres = static_cast<uint8_t*>(L.res.p);
         uint8_t* scr = static_cast<uint8_t*>(L.scratch.p);
@@ -799,6 +801,10 @@ int zg_dev_cdc(zg_ctx* ctx, const uint8_t* d_data, uint64_t len, uint64_t* d_end
     CU(launch_cdc(d_data, len, d_ends, cap, d_n_out, d_scratch, scratch_bytes, static_cast<cudaStream_t>(stream)));
     ctx->kernels += 2;
     return ZG_OK;
+}
+
+void zg_chunk_order(zg_chunk_desc* descs, size_t n) {
+    if (descs && n) fill_decode_order(reinterpret_cast<ChunkDesc*>(descs), n);
 }
 
 int zg_get_stats(zg_ctx* ctx, zg_stats* out) {

@@ -47,8 +47,10 @@ struct ChunkDesc {      // one per chunk, built by the host walk (zg_xorb_index)
     uint32_t clen;
     uint32_t ulen;
     uint32_t scheme;    // 0 none, 1 lz4 frame, 2 bg4 + lz4 frame
-    uint32_t pad;
+    uint32_t order;     // work order: the t-th chunk handed out is chunks[t].order (a permutation; longest first)
 };
+// Fill chunks[t].order so that work is handed out longest-first (keeps the last warps from finishing alone).
+void fill_decode_order(ChunkDesc* chunks, size_t n);
 size_t decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes);
 cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkDesc* chunks, size_t n, uint8_t* out,
                           uint64_t out_bytes, int32_t* status, void* scratch, size_t scratch_bytes, cudaStream_t st);

@@ -22,7 +22,9 @@
 //
 // Roofline: HBM-bound in principle (compressed bytes in + decoded bytes out); in practice bounded by issue slots
 // and L1 wavefronts per sequence.  bench.py reports achieved GB/s over those algorithmic bytes.
+#include <algorithm>
 #include <cstdlib>
+#include <vector>
 
 #include "kernels.h"
 
@@ -30,7 +32,7 @@ namespace zg {
 
 namespace {
 
-constexpr int kWarps = 4;          // warps per CTA
+constexpr int kWarps = 1;          // warps per CTA (no block-level cooperation; small CTAs spread over all SMs)
 constexpr int kSeqCap = 16;        // records parsed per slot per round (two slots share one 32-lane execute step)
 constexpr uint32_t kShort = 16;    // literal runs / matches up to this length are copied by their own lane
 constexpr uint32_t kMaxPiece = 65535;
@@ -50,6 +52,7 @@ struct WarpShared {
     unsigned long long lz[32];     // per slot: LZ4 output base
     uint32_t pend[32];             // per slot: records whose match is still to be copied (bit s)
     uint32_t frontier[32];         // per slot: output offset below which everything is final this round
+    uint32_t w0[32];               // per slot: output offset where this round's records start
     uint8_t first[32];             // per slot: index of the first pending match
     uint8_t cnt[32];               // per slot: records parsed this round
 };
@@ -142,18 +145,45 @@ __device__ __forceinline__ void warp_match(uint8_t* dst, uint32_t off, uint32_t 
     }
 }
 
-// out[4j+k] = plane_k[j]  (SURVEY.md A.4).  tmp holds the four planes back to back.
+// Four bytes at any alignment (two aligned words + funnel shift).
+__device__ __forceinline__ uint32_t ld4_unaligned(const uint8_t* p) {
+    uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+    uint32_t sh = (uint32_t)(a & 3) * 8;
+    uint32_t lo = w[0], hi = sh ? w[1] : 0u;
+    return __funnelshift_r(lo, hi, sh);
+}
+
+// out[4j+k] = plane_k[j]  (SURVEY.md A.4).  tmp holds the four planes back to back.  Each lane turns 4 bytes of
+// every plane into 16 output bytes with a 4x4 byte transpose (8 PRMT) and one 16-byte store when the destination
+// allows it (the verify layout always does).
 __device__ __forceinline__ void warp_regroup(uint8_t* out, const uint8_t* tmp, uint32_t n, uint32_t lane) {
-    uint32_t q = n >> 2, r = n & 3;
-    uint32_t p1 = q + (0 < r), p2 = p1 + q + (1 < r), p3 = p2 + q + (2 < r);
-    if ((reinterpret_cast<uintptr_t>(out) & 3) == 0) {
-        uint32_t* o = reinterpret_cast<uint32_t*>(out);
-        for (uint32_t j = lane; j < q; j += 32)
-            o[j] = (uint32_t)tmp[j] | ((uint32_t)tmp[p1 + j] << 8) | ((uint32_t)tmp[p2 + j] << 16) | ((uint32_t)tmp[p3 + j] << 24);
-    } else {
-        for (uint32_t j = lane; j < q; j += 32) {
-            out[4 * j] = tmp[j]; out[4 * j + 1] = tmp[p1 + j]; out[4 * j + 2] = tmp[p2 + j]; out[4 * j + 3] = tmp[p3 + j];
+    const uint32_t q = n >> 2, r = n & 3;
+    const uint32_t p1 = q + (0 < r), p2 = p1 + q + (1 < r), p3 = p2 + q + (2 < r);
+    const uint32_t q4 = q >> 2;  // groups of four quads = 16 output bytes
+    const uint32_t oa = (uint32_t)(reinterpret_cast<uintptr_t>(out) & 15);
+    for (uint32_t g = lane; g < q4; g += 32) {
+        const uint32_t j = 4 * g;
+        const uint32_t a = ld4_unaligned(tmp + j), b = ld4_unaligned(tmp + p1 + j), c = ld4_unaligned(tmp + p2 + j),
+                       d = ld4_unaligned(tmp + p3 + j);
+        const uint32_t t0 = __byte_perm(a, b, 0x5140), t1 = __byte_perm(a, b, 0x7362);
+        const uint32_t u0 = __byte_perm(c, d, 0x5140), u1 = __byte_perm(c, d, 0x7362);
+        const uint32_t o0 = __byte_perm(t0, u0, 0x5410), o1 = __byte_perm(t0, u0, 0x7632);
+        const uint32_t o2 = __byte_perm(t1, u1, 0x5410), o3 = __byte_perm(t1, u1, 0x7632);
+        uint8_t* o = out + 16 * (size_t)g;
+        if (oa == 0) *reinterpret_cast<uint4*>(o) = make_uint4(o0, o1, o2, o3);
+        else if ((oa & 3) == 0) {
+            uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+            ow[0] = o0; ow[1] = o1; ow[2] = o2; ow[3] = o3;
+        } else {
+            const uint32_t v[4] = {o0, o1, o2, o3};
+#pragma unroll
+            for (int i = 0; i < 16; i++) o[i] = (uint8_t)(v[i >> 2] >> (8 * (i & 3)));
         }
+    }
+    // the last 0..3 quads and the 0..3 odd bytes
+    for (uint32_t j = 4 * q4 + lane; j < q; j += 32) {
+        out[4 * j] = tmp[j]; out[4 * j + 1] = tmp[p1 + j]; out[4 * j + 2] = tmp[p2 + j]; out[4 * j + 3] = tmp[p3 + j];
     }
     if (lane == 0) {
         if (r > 0) out[4 * q] = tmp[q];
@@ -180,7 +210,16 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
     uint32_t p_lit = 0, p_lsrc = 0, p_mlen = 0, p_off = 0;
     int err = 0;
 
+#ifdef ZG_LZ4_PROFILE
+    long long t_parse = 0, t_p1 = 0, t_p2 = 0, t_fin = 0, n_rounds = 0, n_p2 = 0, tq;
+#define ZG_T0() tq = clock64()
+#define ZG_T(acc) do { long long now__ = clock64(); acc += now__ - tq; tq = now__; } while (0)
+#else
+#define ZG_T0()
+#define ZG_T(acc)
+#endif
     for (;;) {
+        ZG_T0();
         // ---- refill idle slots from the ticket counter
         uint32_t idle = __ballot_sync(0xffffffffu, state == ST_IDLE);
         if (idle) {
@@ -191,8 +230,9 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
             if (state == ST_IDLE) {
                 uint32_t t = base + __popc(idle & ((1u << lane) - 1));
                 if (t < n_chunks) {
-                    ChunkDesc d = chunks[t];
-                    ci = t; clen = d.clen; ulen = d.ulen; scheme = d.scheme;
+                    const uint32_t k = chunks[t].order;  // longest-first work order (fill_decode_order)
+                    ChunkDesc d = chunks[k < n_chunks ? k : t];
+                    ci = k < n_chunks ? k : t; clen = d.clen; ulen = d.ulen; scheme = d.scheme;
                     src = comp + d.src_off;
                     fin_out = out + d.dst_off;
                     lz = scheme == 2 ? tmp + d.dst_off : fin_out;
@@ -208,11 +248,61 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
 
         // ---- parse: every active lane appends up to kSeqCap records for its own chunk
         uint32_t cnt = 0, pmask = 0;
+        ws.w0[lane] = op;
         bool finished = false;  // chunk complete (ok or error) after this round's records
-        // Control flow matters here: lanes run in lock-step only while they take the same path, so the common case
-        // (one LZ4 sequence -> one record) is a single straight-line iteration; block/frame boundaries, oversized
-        // pieces and errors leave it for the state machine below and rejoin on the next iteration.
-        while (cnt < (uint32_t)kSeqCap && state != ST_IDLE && state != ST_EXHAUSTED && !finished) {
+        // Lock-step matters: lanes execute together only while they follow the same path, and a lane that falls behind
+        // would otherwise finish its quota alone.  So the loop runs a fixed number of steps for the whole warp and every
+        // active lane makes ONE step per iteration -- normally one sequence on the hot path; block/frame boundaries,
+        // length-extension bytes, oversized pieces and errors take the general path of that iteration and rejoin.
+        uint32_t wv0 = 0, wv1 = 0, wv2 = 0, wip = 0xffffffffu;  // raw words of the 8-byte window at position wip
+#pragma unroll 1
+        for (int step = 0; step < kSeqCap; step++) {
+            const bool act = !finished && state != ST_IDLE && state != ST_EXHAUSTED;
+            if (!__any_sync(0xffffffffu, act)) break;
+            if (!act) continue;
+            bool handled = false;
+            if (state == ST_IN_BLOCK && (p_lit | p_mlen) == 0 && bend - ip >= 48 && ulen - op >= 40) {
+                // Hot path: far from the end of the block and of the output.  If there are no length-extension bytes the
+                // only checks left of the oracle's list are those on the offset; the rest is implied by the two margins
+                // (such a sequence consumes <= 17 input bytes and produces <= 32 output bytes).  Software-pipelined: the
+                // serial chain is window -> token -> literal length -> next position -> next window, so the next
+                // window's words are requested as soon as the literal length is known, carried RAW into the next step,
+                // and the record bookkeeping runs in the shadow of that load.
+                const uintptr_t a = reinterpret_cast<uintptr_t>(src + ip);
+                if (wip != ip) {
+                    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+                    wv0 = __ldg(w); wv1 = __ldg(w + 1); wv2 = __ldg(w + 2);
+                }
+                const uint32_t sh0 = (uint32_t)(a & 3) * 8;
+                const uint32_t lo = __funnelshift_r(wv0, wv1, sh0), hi = __funnelshift_r(wv1, wv2, sh0);
+                const uint32_t tok = lo & 0xffu;
+                const uint32_t lit = tok >> 4, mln = tok & 15u;
+                if (lit != 15u && mln != 15u) {
+                    const uint32_t nip = ip + 3 + lit;
+                    const uint32_t* nw = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(src + nip) & ~(uintptr_t)3);
+                    const uint32_t n0 = __ldg(nw), n1 = __ldg(nw + 1), n2 = __ldg(nw + 2);
+                    uint32_t off;
+                    if (lit <= 5) {
+                        const uint32_t sh = 8 + 8 * lit;
+                        off = (sh < 32 ? __funnelshift_r(lo, hi, sh) : (hi >> (sh - 32))) & 0xffffu;
+                    } else
+                        off = rd8(src + ip + 1 + lit) | (rd8(src + ip + 2 + lit) << 8);
+                    const uint32_t vop = op + lit, ml = mln + 4;
+                    if (off == 0 || off > vop - win_lo) { err = E_LZ4_BLOCK; finished = true; }
+                    else {
+                        Seq e{ip + 1, op, lit | (ml << 16), off};
+                        ws.rec[cnt * 32 + (lane ^ cnt)] = e;
+                        pmask |= 1u << cnt;
+                        cnt++;
+                        op = vop + ml;
+                        ip = nip;
+                        wv0 = n0; wv1 = n1; wv2 = n2; wip = nip;
+                    }
+                    handled = true;
+                }
+            }
+            if (handled) continue;
+            wip = 0xffffffffu;
             if (state == ST_IN_BLOCK && (p_lit | p_mlen) == 0) {
                 // One sequence.  The checks and their order are those of the oracle's lz4_block; the bytes come from
                 // an 8-byte window fetched with one round trip (token, short literal run and offset usually all sit
@@ -352,10 +442,13 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
         ws.cnt[lane] = (uint8_t)cnt;
         ws.pend[lane] = pmask;
         __syncwarp();
+        ZG_T(t_parse);
         const uint32_t have = __ballot_sync(0xffffffffu, cnt > 0);  // slots with records this round
 
-        // ---- execute, pass L: every literal run of every slot (independent of each other).  A 32-lane step covers
-        // two slots x 16 records; two steps are issued back to back so four slots' loads are in flight at once.
+        // ---- execute, pass 1: every literal run, and every match whose source lies wholly before this round's
+        // output (no dependence on anything written this round: ~91 % of matches on text, ~98 % on byte-grouped
+        // bf16).  A 32-lane step covers two slots x 16 records; two steps are issued back to back so the loads of four
+        // slots (literal + match source each) are in flight together.
         const uint32_t half = lane >> 4, s = lane & 15;
 #pragma unroll 1
         for (uint32_t it = 0; it < 16; it += 2) {
@@ -365,16 +458,27 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
             if (s < ws.cnt[cA]) eA = ws.rec[s * 32 + (cA ^ s)];
             if (s < ws.cnt[cB]) eB = ws.rec[s * 32 + (cB ^ s)];
             const uint32_t litA = eA.lens & 0xffffu, litB = eB.lens & 0xffffu;
+            const uint32_t mlA = eA.lens >> 16, mlB = eB.lens >> 16;
             const uint8_t* sA = reinterpret_cast<const uint8_t*>(ws.src[cA]) + eA.lit_src;
             const uint8_t* sB = reinterpret_cast<const uint8_t*>(ws.src[cB]) + eB.lit_src;
             uint8_t* dA = reinterpret_cast<uint8_t*>(ws.lz[cA]) + eA.dst;
             uint8_t* dB = reinterpret_cast<uint8_t*>(ws.lz[cB]) + eB.dst;
-            uint32_t xA[4], xB[4];
             const uint32_t nA = litA <= kShort ? litA : 0u, nB = litB <= kShort ? litB : 0u;
+            // "old" match: short, and its source ends at or before the first byte this round produces for the slot
+            const bool oldA = mlA != 0 && mlA <= kShort && eA.dst + litA - eA.off + mlA <= ws.w0[cA];
+            const bool oldB = mlB != 0 && mlB <= kShort && eB.dst + litB - eB.off + mlB <= ws.w0[cB];
+            const uint32_t kA = oldA ? mlA : 0u, kB = oldB ? mlB : 0u;
+            uint32_t xA[4], xB[4], yA[4], yB[4];
             load16<true>(sA, nA, xA);
             load16<true>(sB, nB, xB);
+            load16<false>(dA + litA - eA.off, kA, yA);
+            load16<false>(dB + litB - eB.off, kB, yB);
             store16(dA, nA, xA);
             store16(dB, nB, xB);
+            store16(dA + litA, kA, yA);
+            store16(dB + litB, kB, yB);
+            if (oldA) atomicAnd(&ws.pend[cA], ~(1u << s));
+            if (oldB) atomicAnd(&ws.pend[cB], ~(1u << s));
             uint32_t lA = __ballot_sync(0xffffffffu, litA > kShort), lB = __ballot_sync(0xffffffffu, litB > kShort);
             while (lA) {
                 int l = __ffs(lA) - 1;
@@ -392,10 +496,11 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
             }
         }
         __syncwarp();
+        ZG_T(t_p1);
 
-        // ---- execute, pass M: matches.  Per slot they are ordered; a match may run as soon as its source lies below
-        // the slot's frontier (start of the first match still pending), so every round retires at least one match per
-        // slot and usually most of them.
+        // ---- execute, pass 2: the matches that read this round's own output.  Per slot they are ordered; a match may
+        // run as soon as its source lies below the slot's frontier (start of the first match still pending), so every
+        // round retires at least one match per slot and usually most of them.
         for (;;) {
             uint32_t p = ws.pend[lane];
             if (p) {
@@ -407,6 +512,9 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
             const uint32_t anyp = __ballot_sync(0xffffffffu, p != 0);
             if (!anyp) break;
             __syncwarp();
+#ifdef ZG_LZ4_PROFILE
+            n_p2++;
+#endif
 #pragma unroll 1
             for (uint32_t it = 0; it < 16; it += 2) {
                 if (((anyp >> (2 * it)) & 0xfu) == 0) continue;
@@ -450,6 +558,7 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
             __syncwarp();
         }
 
+        ZG_T(t_p2);
         // ---- chunks that finished this round: regroup (scheme 2) and publish the status
         uint32_t fin = __ballot_sync(0xffffffffu, finished);
         while (fin) {
@@ -468,10 +577,31 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
             state = ST_IDLE;
         }
         __syncwarp();
+        ZG_T(t_fin);
+#ifdef ZG_LZ4_PROFILE
+        n_rounds++;
+#endif
     }
+#ifdef ZG_LZ4_PROFILE
+    if (lane == 0) {
+        unsigned long long* pr = reinterpret_cast<unsigned long long*>(ticket) + 2;
+        atomicAdd(pr + 0, (unsigned long long)t_parse); atomicAdd(pr + 1, (unsigned long long)t_p1);
+        atomicAdd(pr + 2, (unsigned long long)t_p2); atomicAdd(pr + 3, (unsigned long long)t_fin);
+        atomicAdd(pr + 4, (unsigned long long)n_rounds); atomicAdd(pr + 5, (unsigned long long)n_p2);
+    }
+#endif
 }
 
 }  // namespace
+
+void fill_decode_order(ChunkDesc* chunks, size_t n) {
+    std::vector<uint32_t> idx(n);
+    for (size_t i = 0; i < n; i++) idx[i] = (uint32_t)i;
+    std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) {
+        return (uint64_t)chunks[a].clen + chunks[a].ulen > (uint64_t)chunks[b].clen + chunks[b].ulen;
+    });
+    for (size_t t = 0; t < n; t++) chunks[t].order = idx[t];
+}
 
 size_t decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes) {
     (void)n_chunks;
@@ -489,16 +619,20 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     cudaError_t e = cudaMemsetAsync(ticket, 0, 256, st);
     if (e != cudaSuccess) return e;
     // Slots (chunks in flight) per warp: few when the batch is small, so that every SM gets several warps; up to 32
-    // for large batches, where the serial token walk is then spread over all lanes.  ZEST_LZ4_SLOTS /
-    // ZEST_LZ4_WARPS override the heuristic (tuning knobs).
-    size_t want_warps = 148 * 12, max_warps = 148 * 16;
+    // for large batches, where the serial token walk is then spread over all lanes.  Chunks are handed out
+    // longest-first through the ticket counter, so the launch keeps fewer slots than chunks (`oversub` chunks per slot
+    // on average): a slot that finishes a long chunk picks up a short one and the tail stays balanced.
+    // ZEST_LZ4_SLOTS / ZEST_LZ4_WARPS / ZEST_LZ4_OVERSUB override the heuristic (tuning knobs).
+    size_t want_warps = 148 * 12, max_warps = 148 * 16, oversub = 2;
     if (const char* e = getenv("ZEST_LZ4_WARPS")) { long v = atol(e); if (v > 0) want_warps = max_warps = (size_t)v; }
-    uint32_t slots = (uint32_t)((n + want_warps - 1) / want_warps);
+    if (const char* e = getenv("ZEST_LZ4_OVERSUB")) { long v = atol(e); if (v > 0) oversub = (size_t)v; }
+    uint32_t slots = (uint32_t)((n + want_warps * oversub - 1) / (want_warps * oversub));
     if (const char* e = getenv("ZEST_LZ4_SLOTS")) { long v = atol(e); if (v > 0) slots = (uint32_t)v; }
     if (slots < 1) slots = 1;
     if (slots > 32) slots = 32;
-    size_t warps = (n + slots - 1) / slots;
+    size_t warps = (n + slots * oversub - 1) / (slots * oversub);
     if (warps > max_warps) warps = max_warps;
+    if (warps < 1) warps = 1;
     unsigned blocks = (unsigned)((warps + kWarps - 1) / kWarps);
     lz4_decode_kernel<<<blocks, kWarps * 32, 0, st>>>(comp, chunks, (uint32_t)n, out, tmp, status, ticket, slots);
     return cudaGetLastError();
