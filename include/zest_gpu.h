@@ -175,7 +175,7 @@ ZG_API int zg_dev_verify_xorbs(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp
                         void* d_scratch, size_t scratch_bytes, void* stream);
 
 ZG_API size_t zg_dev_cdc_scratch_bytes(uint64_t len);
-/* d_n_out: two u64 {number of cuts, overflow flag}. */
+/* d_n_out: four u64 {number of cuts, overflow flag, 2 x internal}. */
 ZG_API int zg_dev_cdc(zg_ctx* ctx, const uint8_t* d_data, uint64_t len, uint64_t* d_ends, uint64_t cap, uint64_t* d_n_out,
                void* d_scratch, size_t scratch_bytes, void* stream);
 

@@ -138,7 +138,7 @@ def main():
         n = raw.numel()
         cap = n // 8192 + 2
         d_ends = torch.zeros(cap, dtype=torch.int64, device=dev)
-        d_n = torch.zeros(2, dtype=torch.int64, device=dev)
+        d_n = torch.zeros(4, dtype=torch.int64, device=dev)
         s_cdc = torch.empty(L.zg_dev_cdc_scratch_bytes(n), dtype=torch.uint8, device=dev)
         f = lambda: check(L.zg_dev_cdc(ctx.handle, raw.data_ptr(), n, d_ends.data_ptr(), cap, d_n.data_ptr(), s_cdc.data_ptr(), s_cdc.numel(), sp))
         ms = timed(f, args.steps)

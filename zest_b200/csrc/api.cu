@@ -6,6 +6,7 @@
 #include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -29,6 +30,17 @@ int fail(int code, const char* fmt, ...) {
     va_end(ap);
     return code;
 }
+}  // namespace
+namespace zg {
+int set_last_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+}  // namespace zg
+namespace {
 int cuda_fail(cudaError_t e, const char* what) {
     int code = (e == cudaErrorMemoryAllocation) ? ZG_ERR_OOM : ZG_ERR_CUDA;
     return fail(code, "%s: %s", what, cudaGetErrorString(e));
@@ -379,7 +391,14 @@ struct VerifySlot {
     std::vector<uint64_t> ulen_total;  // per xorb
 };
 
-constexpr uint64_t kSubBatchBytes = 256ull << 20;
+uint64_t sub_batch_bytes() {  // ZEST_VERIFY_SUBBATCH_MB: tuning knob
+    static const uint64_t v = []() { const char* e = getenv("ZEST_VERIFY_SUBBATCH_MB"); long m = e ? atol(e) : 0; return (uint64_t)(m > 0 ? m : 128) << 20; }();
+    return v;
+}
+int max_verify_lanes() {  // ZEST_VERIFY_LANES: tuning knob
+    static const int v = []() { const char* e = getenv("ZEST_VERIFY_LANES"); long m = e ? atol(e) : 0; return (int)(m > 0 && m < 4 ? m : 4); }();
+    return v;
+}
 
 }  // namespace
 
@@ -392,13 +411,16 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
     if (bytes_verified) *bytes_verified = 0;
     if (n == 0) return ZG_OK;
     ctx->calls++;
-    // Up to two lanes: the copies of one sub-batch overlap the kernels of the other, and the host walk of the
-    // next sub-batch overlaps both.
-    LaneGuard g0(ctx), g1(ctx, false);
-    VerifySlot slots[2];
-    slots[0].L = g0.l;
-    slots[1].L = g1.l;
-    const int n_slots = g1.l ? 2 : 1;
+    // Up to four lanes: the copies of one sub-batch overlap the kernels of the others and the host walk of the next.
+    // Several sub-batches in flight also matter for the decoder itself: one LZ4 chunk is a serial chain of a few
+    // milliseconds, so a single ~128 MB sub-batch cannot fill the GPU; three or four of them on separate streams do.
+    constexpr int kMaxSlots = 4;
+    LaneGuard g0(ctx), g1(ctx, false), g2(ctx, false), g3(ctx, false);
+    VerifySlot slots[kMaxSlots];
+    Lane* got[kMaxSlots] = {g0.l, g1.l, g2.l, g3.l};
+    int n_slots = 0;
+    for (int i = 0; i < kMaxSlots && n_slots < max_verify_lanes(); i++)
+        if (got[i]) slots[n_slots++].L = got[i];
     size_t hashes_written = 0;
     uint64_t verified = 0;
 
@@ -430,7 +452,7 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         std::vector<uint64_t> utot;
         size_t x0 = x, nc = 0;
         uint64_t ub = 0, cb = 0;
-        while (x < n && (x == x0 || ub < kSubBatchBytes)) {
+        while (x < n && (x == x0 || ub < sub_batch_bytes())) {
             ixs.emplace_back();
             uint32_t c = 0;
             int wr = (!blobs[x] && lens[x]) ? ZG_ERR_INVALID_ARG : walk(blobs[x], lens[x], 0xffffffffu, &ixs.back(), &c);

@@ -109,123 +109,228 @@ __global__ void __launch_bounds__(kThreads) cdc_scan_kernel(const uint8_t* __res
     }
 }
 
-// Serial part: min/max rule over the sparse candidate stream.  One warp; all lanes hold the same walker state,
-// lanes load 32 tile records at a time.
-struct Walker {
-    uint64_t s;      // current chunk start
-    uint64_t n;      // cuts emitted
-    uint64_t cap;
-    uint64_t* ends;
+// ---------------------------------------------------------------------------------------------------------------
+// Pass 2: the min/max rule over the sparse candidate stream.  The rule is a chain (each cut depends on the previous
+// one), but the chain forgets quickly: a walker started at an arbitrary position agrees with the true one as soon as
+// both cut at the same candidate, usually within one or two chunks.  So the tile list is split into segments; every
+// segment is walked speculatively (as if a cut fell exactly on its first byte) by its own thread, and a single thread
+// then stitches: it carries the true state into each segment, walks until one of its cuts equals one of the
+// segment's speculative cuts, and adopts the rest of that list.  A last kernel gathers the pieces in order.
+// ---------------------------------------------------------------------------------------------------------------
+
+struct SegInfo {       // 32 bytes per segment
+    uint32_t spec_n;   // speculative cuts found
+    uint32_t cand_n;   // candidates seen in the segment (0 => only forced cuts, handled arithmetically)
+    uint32_t dense;    // a tile overflowed its hit list: the stitcher walks this segment itself
+    uint32_t join;     // stitcher: index in the speculative list from which it is adopted
+    uint32_t priv_n;   // stitcher: cuts before the join that differ from the speculation
+    uint32_t pad;
+    uint64_t base;     // stitcher: position of the segment's first cut in the output
+};
+
+struct CutSink {  // where a walker puts its cuts
+    uint64_t* buf;
+    uint32_t n, cap;
     bool overflow;
-    __device__ void emit(uint64_t e, uint32_t lane) {
-        if (n < cap) { if (lane == 0) ends[n] = e; }
-        else overflow = true;
+    __device__ void put(uint64_t e) {
+        if (n < cap) buf[n] = e; else overflow = true;
         n++;
-        s = e;
-    }
-    __device__ void candidate(uint64_t e, uint32_t lane) {  // e = end offset (position + 1)
-        while (e - s > kMax) emit(s + kMax, lane);
-        if (e - s >= kMin) emit(e, lane);
     }
 };
 
-__device__ __forceinline__ void load_tile_rec(const TileRec* __restrict__ tiles, uint64_t t, uint64_t n_tiles, uint4& a, uint4& b) {
-    a = make_uint4(0, 0, 0, 0);
-    b = a;
-    if (t < n_tiles) {
+__device__ __forceinline__ uint32_t tile_pos(const uint4& a, const uint4& b, int i) {
+    const uint32_t ww[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    return (ww[(i + 2) >> 1] >> (16 * ((i + 2) & 1))) & 0xffffu;
+}
+
+// Apply the rule to one candidate end offset e for a walker in state s; cuts go to `put`.
+template <typename Put>
+__device__ __forceinline__ void rule_candidate(uint64_t& s, uint64_t e, Put&& put) {
+    while (e - s > kMax) { s += kMax; put(s); }
+    if (e - s >= kMin) { s = e; put(s); }
+}
+
+__global__ void __launch_bounds__(128) cdc_spec_kernel(const TileRec* __restrict__ tiles, uint64_t n_tiles,
+                                                       uint64_t len, uint32_t seg_tiles, uint32_t n_segs,
+                                                       uint32_t cap, SegInfo* __restrict__ segs,
+                                                       uint64_t* __restrict__ spec) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_segs) return;
+    const uint64_t t0 = (uint64_t)k * seg_tiles, t1 = t0 + seg_tiles < n_tiles ? t0 + seg_tiles : n_tiles;
+    const uint64_t seg_end = t1 * (uint64_t)kTileBytes < len ? t1 * (uint64_t)kTileBytes : len;
+    uint64_t s = t0 * (uint64_t)kTileBytes;
+    CutSink sink{spec + (size_t)k * cap, 0, cap, false};
+    uint32_t cand = 0, dense = 0;
+    for (uint64_t t = t0; t < t1; t++) {
         const uint4* q = reinterpret_cast<const uint4*>(tiles + t);
-        a = __ldg(q);
-        b = __ldg(q + 1);
+        const uint4 a = __ldg(q);
+        const uint32_t c = a.x & 0xffffu;
+        if (c == 0) continue;
+        if (c > (uint32_t)kListCap) { dense = 1; break; }
+        const uint4 b = __ldg(q + 1);
+        cand += c;
+        const uint64_t tb = t * (uint64_t)kTileBytes;
+        for (uint32_t i = 0; i < c; i++) rule_candidate(s, tb + tile_pos(a, b, (int)i) + 1, [&](uint64_t e) { sink.put(e); });
+    }
+    if (!dense) while (seg_end - s >= kMax && seg_end > s) { s += kMax; sink.put(s); }
+    SegInfo r;
+    r.spec_n = dense || sink.overflow ? 0u : sink.n;
+    r.cand_n = cand;
+    r.dense = dense || sink.overflow;
+    r.join = 0; r.priv_n = 0; r.pad = 0; r.base = 0;
+    segs[k] = r;
+}
+
+// True walk of tiles [t0, t1) from state s, with dense tiles re-scanned; every cut goes to `put`, which returns true
+// to stop (the stitcher stops at the join).  Returns true if stopped.
+template <typename Put>
+__device__ bool walk_tiles(const uint8_t* __restrict__ data, uint64_t len, const TileRec* __restrict__ tiles,
+                           uint64_t t0, uint64_t t1, uint64_t& s, Put&& put) {
+    bool stop = false;
+    for (uint64_t t = t0; t < t1 && !stop; t++) {
+        const uint4* q = reinterpret_cast<const uint4*>(tiles + t);
+        const uint4 a = __ldg(q);
+        const uint32_t c = a.x & 0xffffu;
+        if (c == 0) continue;
+        const uint64_t tb = t * (uint64_t)kTileBytes;
+        if (c <= (uint32_t)kListCap) {
+            const uint4 b = __ldg(q + 1);
+            for (uint32_t i = 0; i < c && !stop; i++)
+                rule_candidate(s, tb + tile_pos(a, b, (int)i) + 1, [&](uint64_t e) { if (!stop) stop = put(e); });
+        } else {
+            // dense tile: roll the hash again, but only from where a cut may next fall
+            const uint64_t tend = tb + kTileBytes < len ? tb + kTileBytes : len;
+            uint64_t p = tb;
+            while (p < tend && !stop) {
+                while (p + 1 - s > kMax && !stop) { s += kMax; stop = put(s); }
+                if (stop) break;
+                if (p + 1 - s < kMin) p = s + kMin - 1;
+                if (p >= tend) break;
+                uint64_t h = 0;
+                for (uint64_t x = p >= 63 ? p - 63 : 0; x <= p; x++) h = (h << 1) + kGear[data[x]];
+                for (;;) {
+                    if ((h >> 48) == 0) {
+                        rule_candidate(s, p + 1, [&](uint64_t e) { if (!stop) stop = put(e); });
+                        p++;
+                        break;
+                    }
+                    p++;
+                    if (p >= tend) break;
+                    if (p + 1 - s > kMax) break;
+                    h = (h << 1) + kGear[data[p]];
+                }
+            }
+        }
+    }
+    return stop;
+}
+
+__global__ void __launch_bounds__(32) cdc_stitch_kernel(const uint8_t* __restrict__ data, uint64_t len,
+                                                        const TileRec* __restrict__ tiles, uint64_t n_tiles,
+                                                        uint32_t seg_tiles, uint32_t n_segs, uint32_t cap,
+                                                        SegInfo* __restrict__ segs, const uint64_t* __restrict__ spec,
+                                                        uint64_t* __restrict__ priv, uint64_t* __restrict__ n_out,
+                                                        uint64_t out_cap) {
+    if (threadIdx.x != 0) return;
+    uint64_t s = 0, total = 0;
+    bool overflow = false;
+    for (uint32_t k = 0; k < n_segs; k++) {
+        const uint64_t t0 = (uint64_t)k * seg_tiles, t1 = t0 + seg_tiles < n_tiles ? t0 + seg_tiles : n_tiles;
+        const uint64_t seg_end = t1 * (uint64_t)kTileBytes < len ? t1 * (uint64_t)kTileBytes : len;
+        SegInfo g = segs[k];
+        const uint64_t* sp = spec + (size_t)k * cap;
+        CutSink pv{priv + (size_t)k * cap, 0, cap, false};
+        uint32_t j = 0;
+        bool joined = false;
+        auto put = [&](uint64_t e) -> bool {
+            if (!g.dense) {
+                while (j < g.spec_n && sp[j] < e) j++;
+                if (j < g.spec_n && sp[j] == e) { joined = true; return true; }
+            }
+            pv.put(e);
+            return false;
+        };
+        if (s == t0 * (uint64_t)kTileBytes && !g.dense) {
+            joined = true;  // the speculation started from the true state (always so for segment 0)
+            j = 0;
+        } else {
+            if (g.cand_n != 0 || g.dense) walk_tiles(data, len, tiles, t0, t1, s, put);
+            if (!joined) while (seg_end - s >= kMax && seg_end > s && !joined) { s += kMax; if (put(s)) break; }
+        }
+        g.base = total;
+        g.priv_n = pv.n;
+        g.join = joined ? j : g.spec_n;
+        if (pv.overflow) overflow = true;
+        total += pv.n + (g.spec_n - g.join);
+        if (joined && g.spec_n > g.join) s = sp[g.spec_n - 1];
+        segs[k] = g;
+    }
+    // whatever is left after the last cut is the final (possibly short) chunk
+    uint64_t extra = 0;
+    uint64_t* tail = priv + (size_t)n_segs * cap;  // room for one more entry
+    if (len > s) { tail[0] = len; extra = 1; }
+    n_out[0] = total + extra;
+    n_out[1] = (overflow || total + extra > out_cap) ? 1 : 0;
+    n_out[2] = total;  // where the tail entry goes
+}
+
+__global__ void __launch_bounds__(128) cdc_gather_kernel(const SegInfo* __restrict__ segs, uint32_t n_segs, uint32_t cap,
+                                                         const uint64_t* __restrict__ spec,
+                                                         const uint64_t* __restrict__ priv,
+                                                         const uint64_t* __restrict__ n_out, uint64_t* __restrict__ ends,
+                                                         uint64_t out_cap) {
+    const uint32_t k = blockIdx.x;
+    if (k == n_segs) {  // the tail entry
+        if (threadIdx.x == 0 && n_out[0] > n_out[2] && n_out[2] < out_cap) ends[n_out[2]] = priv[(size_t)n_segs * cap];
+        return;
+    }
+    const SegInfo g = segs[k];
+    const uint64_t* pv = priv + (size_t)k * cap;
+    const uint64_t* sp = spec + (size_t)k * cap;
+    const uint32_t take = g.spec_n - g.join;
+    for (uint32_t i = threadIdx.x; i < g.priv_n + take; i += blockDim.x) {
+        const uint64_t o = g.base + i;
+        if (o < out_cap) ends[o] = i < g.priv_n ? pv[i] : sp[g.join + (i - g.priv_n)];
     }
 }
 
-__global__ void __launch_bounds__(32) cdc_walk_kernel(const uint8_t* __restrict__ data, uint64_t len,
-                                                      const TileRec* __restrict__ tiles, uint64_t n_tiles,
-                                                      uint64_t* __restrict__ ends, uint64_t cap,
-                                                      uint64_t* __restrict__ n_out) {
-    __shared__ uint64_t s_cand[32 * kListCap];
-    const uint32_t lane = threadIdx.x;
-    Walker w{0, 0, cap, ends, false};
-    uint4 na, nb;
-    load_tile_rec(tiles, lane, n_tiles, na, nb);
-    for (uint64_t t0 = 0; t0 < n_tiles; t0 += 32) {
-        const uint4 a = na, b = nb;
-        load_tile_rec(tiles, t0 + 32 + lane, n_tiles, na, nb);  // next batch's records are in flight while this one is walked
-        const uint32_t cnt = a.x & 0xffffu;
-        const uint32_t ww[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-        const uint64_t tbase = (t0 + lane) * (uint64_t)kTileBytes;
-        const uint32_t dense = __ballot_sync(0xffffffffu, cnt > (uint32_t)kListCap);
-        if (!dense) {
-            // compact the batch's candidates (ascending by construction) into shared memory, then apply the rule
-            uint32_t x = cnt;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
-                if (lane >= (uint32_t)d) x += y;
-            }
-            const uint32_t total = __shfl_sync(0xffffffffu, x, 31);
-            uint32_t o = x - cnt;
-#pragma unroll
-            for (int i = 0; i < kListCap; i++)
-                if ((uint32_t)i < cnt) s_cand[o + i] = tbase + ((ww[(i + 2) >> 1] >> (16 * ((i + 2) & 1))) & 0xffffu) + 1;
-            __syncwarp();
-            for (uint32_t j = 0; j < total; j++) w.candidate(s_cand[j], lane);
-            __syncwarp();
-            continue;
-        }
-        // a dense tile in the batch: take the tiles one by one
-        uint32_t nz = __ballot_sync(0xffffffffu, cnt != 0);
-        while (nz) {
-            int l = __ffs(nz) - 1;
-            nz &= nz - 1;
-            uint32_t c = __shfl_sync(0xffffffffu, cnt, l);
-            uint64_t tb = (t0 + l) * (uint64_t)kTileBytes;
-            if (c <= (uint32_t)kListCap) {
-#pragma unroll
-                for (int i = 0; i < kListCap; i++) {
-                    uint32_t p = __shfl_sync(0xffffffffu, (ww[(i + 2) >> 1] >> (16 * ((i + 2) & 1))) & 0xffffu, l);
-                    if ((uint32_t)i < c) w.candidate(tb + p + 1, lane);
-                }
-            } else {
-                // dense tile: roll the hash again, but only from where a cut may next fall
-                uint64_t tend = tb + kTileBytes < len ? tb + kTileBytes : len;
-                uint64_t p = tb;
-                while (p < tend) {
-                    while (p + 1 - w.s > kMax) w.emit(w.s + kMax, lane);
-                    if (p + 1 - w.s < kMin) p = w.s + kMin - 1;
-                    if (p >= tend) break;
-                    uint64_t h = 0;
-                    for (uint64_t q = p >= 63 ? p - 63 : 0; q <= p; q++) h = (h << 1) + kGear[data[q]];
-                    for (;;) {
-                        if ((h >> 48) == 0) { w.candidate(p + 1, lane); p++; break; }
-                        p++;
-                        if (p >= tend) break;
-                        if (p + 1 - w.s > kMax) break;
-                        h = (h << 1) + kGear[data[p]];
-                    }
-                }
-            }
-        }
-    }
-    while (len - w.s > kMax) w.emit(w.s + kMax, lane);
-    if (len > w.s) w.emit(len, lane);
-    if (lane == 0) { n_out[0] = w.n; n_out[1] = w.overflow ? 1 : 0; }
+struct CdcLayout { size_t tiles, segs, spec, priv, total; uint32_t seg_tiles, n_segs, cap; uint64_t n_tiles; };
+CdcLayout cdc_layout(uint64_t len) {
+    CdcLayout L;
+    L.n_tiles = (len + kTileBytes - 1) / kTileBytes;
+    uint64_t st = (L.n_tiles + 1023) / 1024;  // <= 1024 segments (the stitcher is serial over them), >= 2 MiB each
+    if (st < 64) st = 64;
+    L.seg_tiles = (uint32_t)st;
+    L.n_segs = (uint32_t)((L.n_tiles + st - 1) / st);
+    L.cap = L.seg_tiles * (kTileBytes / kMin) + 4;
+    size_t o = 0;
+    L.tiles = o; o = align_up(o + (size_t)(L.n_tiles + 1) * sizeof(TileRec), 256);
+    L.segs = o; o = align_up(o + (size_t)(L.n_segs + 1) * sizeof(SegInfo), 256);
+    L.spec = o; o = align_up(o + ((size_t)L.n_segs * L.cap + 1) * 8, 256);
+    L.priv = o; o = align_up(o + ((size_t)L.n_segs * L.cap + 2) * 8, 256);
+    L.total = o;
+    return L;
 }
 
 }  // namespace
 
-size_t cdc_scratch_bytes(uint64_t len) {
-    uint64_t n_tiles = (len + kTileBytes - 1) / kTileBytes;
-    return align_up((size_t)(n_tiles + 1) * sizeof(TileRec), 256);
-}
+size_t cdc_scratch_bytes(uint64_t len) { return cdc_layout(len).total; }
 
 cudaError_t launch_cdc(const uint8_t* data, uint64_t len, uint64_t* ends, uint64_t cap, uint64_t* n_out,
                        void* scratch, size_t scratch_bytes, cudaStream_t st) {
-    uint64_t n_tiles = (len + kTileBytes - 1) / kTileBytes;
-    if (scratch_bytes < cdc_scratch_bytes(len) || n_tiles > 0x7fffffffull) return cudaErrorInvalidValue;
-    TileRec* tiles = static_cast<TileRec*>(scratch);
-    if (n_tiles) cdc_scan_kernel<<<(unsigned)n_tiles, kThreads, 0, st>>>(data, len, tiles);
-    cdc_walk_kernel<<<1, 32, 0, st>>>(data, len, tiles, n_tiles, ends, cap, n_out);
+    CdcLayout L = cdc_layout(len);
+    if (scratch_bytes < L.total || L.n_tiles > 0x7fffffffull) return cudaErrorInvalidValue;
+    uint8_t* sb = static_cast<uint8_t*>(scratch);
+    TileRec* tiles = reinterpret_cast<TileRec*>(sb + L.tiles);
+    SegInfo* segs = reinterpret_cast<SegInfo*>(sb + L.segs);
+    uint64_t* spec = reinterpret_cast<uint64_t*>(sb + L.spec);
+    uint64_t* priv = reinterpret_cast<uint64_t*>(sb + L.priv);
+    if (L.n_tiles) {
+        cdc_scan_kernel<<<(unsigned)L.n_tiles, kThreads, 0, st>>>(data, len, tiles);
+        cdc_spec_kernel<<<(L.n_segs + 127) / 128, 128, 0, st>>>(tiles, L.n_tiles, len, L.seg_tiles, L.n_segs, L.cap, segs, spec);
+    }
+    cdc_stitch_kernel<<<1, 32, 0, st>>>(data, len, tiles, L.n_tiles, L.seg_tiles, L.n_segs, L.cap, segs, spec, priv, n_out, cap);
+    cdc_gather_kernel<<<L.n_segs + 1, 128, 0, st>>>(segs, L.n_segs, L.cap, spec, priv, n_out, ends, cap);
     return cudaGetLastError();
 }
 

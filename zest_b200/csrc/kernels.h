@@ -19,6 +19,9 @@ enum : int {
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// Record a failure for zg_last_error() on the calling thread and return `code` (defined in api.cu).
+int set_last_error(int code, const char* fmt, ...);
+
 // ---------------------------------------------------------------------------------------------- hashing
 // Leaves per thread in the leaf kernel (1, 2, 4 or 8), chosen from the batch size: small batches need every
 // leaf on its own thread to fill 148 SMs, large ones amortise the tree by folding 8 KiB per thread.

@@ -618,12 +618,13 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     uint8_t* tmp = sb + 256;
     cudaError_t e = cudaMemsetAsync(ticket, 0, 256, st);
     if (e != cudaSuccess) return e;
-    // Slots (chunks in flight) per warp: few when the batch is small, so that every SM gets several warps; up to 32
-    // for large batches, where the serial token walk is then spread over all lanes.  Chunks are handed out
-    // longest-first through the ticket counter, so the launch keeps fewer slots than chunks (`oversub` chunks per slot
-    // on average): a slot that finishes a long chunk picks up a short one and the tail stays balanced.
-    // ZEST_LZ4_SLOTS / ZEST_LZ4_WARPS / ZEST_LZ4_OVERSUB override the heuristic (tuning knobs).
-    size_t want_warps = 148 * 12, max_warps = 148 * 16, oversub = 2;
+    // Slots (chunks in flight) per warp: few when the batch is small, so that every SM gets many warps (the token walk
+    // and the copy rounds are latency chains; only other warps hide them); up to 32 for large batches, where the
+    // serial token walk is then spread over all lanes.  Chunks are handed out longest-first through the ticket
+    // counter, and the launch keeps about half as many slots as chunks: a slot that finishes a long chunk picks up
+    // a short one, so the tail stays balanced.  Measured on B200 (profiles/): 8.5k text chunks -> 2 slots, 15.7k
+    // bf16 chunks -> 4 slots.  ZEST_LZ4_SLOTS / ZEST_LZ4_WARPS / ZEST_LZ4_OVERSUB override (tuning knobs).
+    size_t want_warps = 148 * 16, max_warps = 148 * 24, oversub = 2;
     if (const char* e = getenv("ZEST_LZ4_WARPS")) { long v = atol(e); if (v > 0) want_warps = max_warps = (size_t)v; }
     if (const char* e = getenv("ZEST_LZ4_OVERSUB")) { long v = atol(e); if (v > 0) oversub = (size_t)v; }
     uint32_t slots = (uint32_t)((n + want_warps * oversub - 1) / (want_warps * oversub));
