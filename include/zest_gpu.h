@@ -156,6 +156,19 @@ ZG_API int zg_dev_hash_chunks(zg_ctx* ctx, const uint8_t* d_data, uint64_t data_
                        const uint8_t* key /* host pointer, as zg_hash_chunks */, uint8_t* d_out, void* d_scratch,
                        size_t scratch_bytes, void* stream);
 
+/* The same hash pass for callers that cannot allocate device memory: a transfer loop whose memory budget is already
+ * spent on staging and decode buffers, a thread that must not take the driver's allocation lock mid-download, a
+ * process whose allocator is frozen after start-up.  Inputs and outputs are the caller's device buffers, as for
+ * zg_dev_hash_chunks; the working set lives in an 8 MiB array built into the library (held by every GPU that loads
+ * it), enough for any batch of up to 256 MiB of data in up to 65,536 chunks -- a batch whose working set
+ * (zg_dev_hash_scratch_bytes) exceeds the array is refused with ZG_ERR_LIMIT before anything is launched.  Works on the CUDA device that is current on the calling thread; the first call on a device looks up
+ * the array's address and should happen before any stream capture.  Calls on one device share the array: keep them
+ * in order (one stream), overlapping calls race.  Calls no cudaMalloc / cudaFree and no allocating library routine.
+ * This entry point has no counterpart in the reference. */
+ZG_API int zg_dev_hash_chunks_static(const uint8_t* d_data, uint64_t data_bytes, const uint64_t* d_offsets,
+                                     const uint32_t* d_lens, size_t n, const uint8_t* key, uint8_t* d_out,
+                                     void* stream);
+
 ZG_API size_t zg_dev_decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes);
 ZG_API int zg_dev_decode_chunks(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes, const zg_chunk_desc* d_chunks,
                          size_t n_chunks, uint8_t* d_out, uint64_t out_bytes, int32_t* d_status, void* d_scratch,

@@ -16,7 +16,9 @@
 // the input is read exactly once (1 B/B of HBM traffic, >= 4x below the HBM roof at ALU speed).
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 
+#include "../../include/zest_gpu.h"
 #include "kernels.h"
 
 namespace zg {
@@ -344,3 +346,82 @@ cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const u
 }
 
 }  // namespace zg
+
+// ---------------------------------------------------------------------------------------------------------------
+// zg_dev_hash_chunks_static: the chunk-hash pass for callers that must not allocate.
+//
+// Some users of this library run where device allocation is off the table: a transfer loop that has already handed
+// every byte of its memory budget to pinned staging and decode buffers, a host thread that may not take the driver's
+// allocation lock while a download is in flight, or a process whose allocator has been frozen after start-up.  They
+// still own their input and output buffers, but they have nowhere to put the hash pass's working set (the prefix
+// sums, the slot map and the 32-byte group nodes).  For them the library carries that working set itself, in the
+// fixed array below; it is part of the loaded module, so every GPU that loads the library holds these 8 MiB until
+// the process exits, whether or not this entry point is ever called.
+//
+// The array's name is only a host-side handle in host code, not a device address, so the address is looked up once
+// per device with cudaGetSymbolAddress (first call on that device, with the device current) and cached.  That first
+// call therefore does a little set-up work and should be made before any stream capture begins.
+//
+// All calls on a device share the one array and nothing in it survives a call in a useful form.  Nothing has to be
+// cleared between calls: every word the kernels read (prefix sums, map, nodes) is written earlier in the same call.
+// Two calls whose kernels overlap on the GPU (different streams, or different host threads) would race on it, so
+// the caller must keep calls on one device in order, e.g. by issuing them on one stream.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr size_t kStaticScratchBytes = 8u << 20;  // covers any batch up to 256 MiB of data in up to 65,536 chunks
+static __device__ __align__(256) unsigned char g_static_hash_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kMaxDevices] = {nullptr};
+}  // namespace
+
+extern "C" ZG_API int zg_dev_hash_chunks_static(const uint8_t* d_data, uint64_t data_bytes, const uint64_t* d_offsets,
+                                                const uint32_t* d_lens, size_t n, const uint8_t* key, uint8_t* d_out,
+                                                void* stream) {
+    using namespace zg;
+    if (n == 0) return ZG_OK;
+    if (!d_data && data_bytes) return set_last_error(ZG_ERR_INVALID_ARG, "d_data is null");
+    if (!d_offsets || !d_out) return set_last_error(ZG_ERR_INVALID_ARG, "null argument");
+    const int group = hash_pick_group(data_bytes);
+    const size_t need = hash_scratch_bytes(data_bytes, n, group);
+    if (need > kStaticScratchBytes)
+        return set_last_error(ZG_ERR_LIMIT,
+                              "zg_dev_hash_chunks_static: this batch needs %zu bytes of scratch, the built-in array holds %zu "
+                              "(enough for 256 MiB in 65,536 chunks); split the batch or use zg_dev_hash_chunks",
+                              need, kStaticScratchBytes);
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return set_last_error(ZG_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kMaxDevices) return set_last_error(ZG_ERR_LIMIT, "device ordinal %d not supported", dev);
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_ptr[dev]) {  // first call on this device: resolve the array's device address
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_static_hash_scratch);
+            if (e != cudaSuccess || !p) return set_last_error(ZG_ERR_CUDA, "cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            g_static_ptr[dev] = p;
+        }
+        scratch = g_static_ptr[dev];
+    }
+    B3Key k;
+    k.one = 1;
+    if (key == ZG_PLAIN_BLAKE3) {
+        const uint32_t iv[8] = {0x6A09E667u, 0xBB67AE85u, 0x3C6EF372u, 0xA54FF53Au, 0x510E527Fu, 0x9B05688Cu, 0x1F83D9ABu, 0x5BE0CD19u};
+        for (int i = 0; i < 8; i++) k.w[i] = iv[i];
+        k.base_flags = 0;
+    } else {
+        static const uint8_t data_key[32] = {102, 151, 245, 119, 91,  149, 80,  222, 49,  53,  203, 172, 165, 151, 24,  28,
+                                             157, 228, 33,  16,  155, 235, 43,  88,  180, 208, 176, 75,  147, 173, 242, 41};
+        const uint8_t* p = key ? key : data_key;
+        for (int i = 0; i < 8; i++)
+            k.w[i] = (uint32_t)p[4 * i] | ((uint32_t)p[4 * i + 1] << 8) | ((uint32_t)p[4 * i + 2] << 16) | ((uint32_t)p[4 * i + 3] << 24);
+        k.base_flags = B3_KEYED;
+    }
+    e = launch_hash_chunks(d_data, data_bytes, d_offsets, d_lens, n, k, d_out, scratch, kStaticScratchBytes, group,
+                           static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return set_last_error(ZG_ERR_CUDA, "zg_dev_hash_chunks_static launch: %s", cudaGetErrorString(e));
+    return ZG_OK;
+}
+
