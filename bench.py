@@ -126,7 +126,17 @@ def cpu_arm(blobs, expected, total_bytes, threads, min_seconds=3.0, max_reps=20)
     return total_bytes / best / 1e9, best, reps
 
 
+def _claim_stdout():
+    """Keep stdout for the single JSON line: anything libraries print to fd 1 (NCCL's version banner, for one) goes
+    to stderr instead.  Returns a writer for the real stdout."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 def main():
+    out_stream = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -161,14 +171,14 @@ def main():
         dt = time.perf_counter() - t0
         val = total * K / dt / 1e9
         sample = f"all {len(blobs)} xorbs ({total/1e6:.0f} MB uncompressed) per step"
-        print(json.dumps({
+        print(file=out_stream, flush=True, *[json.dumps({
             "impl": "reference", "metric": "xorb verify GB/s (decompress+BLAKE3+Merkle)", "value": round(val, 4), "unit": "GB/s",
             "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": round(dt / K * 1e3, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
             "cpu_baseline": {"value": round(val, 4), "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample,
                              "note": "oracle/xet_oracle.c (CPU restatement; zest's zig-xet path needs a Zig toolchain, absent here)"},
             "e2e": {"value": round(val, 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}))
+            "gpu_launches": 0})])
         return 0
 
     # ------------------------------------------------------------------ our arm
@@ -301,6 +311,7 @@ def main():
 
     if rank != 0:
         ctx.close()
+        zd.shutdown()
         return 0
 
     peaks = {}
@@ -349,8 +360,9 @@ def main():
                 "h2d_GBps": round((s1["h2d_bytes"] - s0["h2d_bytes"]) / t_e2e / 1e9, 2)},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
     }
-    print(json.dumps(out))
+    print(json.dumps(out), file=out_stream, flush=True)
     ctx.close()
+    zd.shutdown()
     return 0
 
 

@@ -640,49 +640,76 @@ OZ_API int64_t oz_verify_xorbs_mt(const uint8_t* const* blobs, const size_t* len
 
 typedef int (*lz4_compress_fn)(const char*, char*, int, int);
 typedef int (*lz4_bound_fn)(int);
+typedef void* (*lz4_create_fn)(void);
+typedef int (*lz4_free_fn)(void*);
+typedef int (*lz4_continue_fn)(void*, const char*, char*, int, int, int);
 static lz4_compress_fn p_compress;
 static lz4_bound_fn p_bound;
+static lz4_create_fn p_create;
+static lz4_free_fn p_free;
+static lz4_continue_fn p_continue;
 static pthread_once_t lz4_once = PTHREAD_ONCE_INIT;
 static void lz4_load(void) {
     void* h = dlopen("liblz4.so.1", RTLD_NOW | RTLD_GLOBAL);
     if (!h) return;
     p_compress = (lz4_compress_fn)dlsym(h, "LZ4_compress_default");
     p_bound = (lz4_bound_fn)dlsym(h, "LZ4_compressBound");
+    p_create = (lz4_create_fn)dlsym(h, "LZ4_createStream");
+    p_free = (lz4_free_fn)dlsym(h, "LZ4_freeStream");
+    p_continue = (lz4_continue_fn)dlsym(h, "LZ4_compress_fast_continue");
 }
 
-/* Frame `ulen` bytes the way lz4_flex does for xet-core (A.4): FLG 0x60, BD 0x40/0x50, HC, blocks of at
- * most block_max bytes (0 = one block of the frame's maximum), EndMark.  Returns frame size. */
-static size_t lz4_frame_encode(const uint8_t* src, size_t ulen, uint8_t* dst, size_t block_max) {
+/* Frame `ulen` bytes the way lz4_flex does for xet-core (A.4): FLG 0x60, BD 0x40/0x50, HC, blocks of at most
+ * block_max bytes (0 = one block of the frame's maximum), EndMark.  `fflags` exercises the optional parts of the
+ * frame format that xet-core does not emit but a decoder must accept (A.4b): 1 content-size field, 2 block
+ * checksums, 4 content checksum, 8 linked blocks (matches may reach into earlier blocks).  Returns frame size. */
+enum { FF_CSIZE = 1, FF_BSUM = 2, FF_CSUM = 4, FF_LINKED = 8 };
+static size_t lz4_frame_encode(const uint8_t* src, size_t ulen, uint8_t* dst, size_t block_max, int fflags) {
     size_t o = 0;
     st32(dst, 0x184D2204u);
-    dst[4] = 0x60;
+    dst[4] = (uint8_t)(0x40 | ((fflags & FF_LINKED) ? 0 : 0x20) | ((fflags & FF_BSUM) ? 0x10 : 0) |
+                       ((fflags & FF_CSIZE) ? 0x08 : 0) | ((fflags & FF_CSUM) ? 0x04 : 0));
     size_t fmax = ulen > 65536 ? 262144 : 65536;
     dst[5] = ulen > 65536 ? 0x50 : 0x40;
-    dst[6] = (uint8_t)(xxh32(dst + 4, 2, 0) >> 8);
-    o = 7;
+    o = 6;
+    if (fflags & FF_CSIZE) {
+        for (int b = 0; b < 8; b++) dst[o + b] = (uint8_t)((uint64_t)ulen >> (8 * b));
+        o += 8;
+    }
+    dst[o] = (uint8_t)(xxh32(dst + 4, o - 4, 0) >> 8);
+    o++;
     if (block_max == 0 || block_max > fmax) block_max = fmax;
+    void* stream = ((fflags & FF_LINKED) && p_create && p_continue) ? p_create() : NULL;
     for (size_t p = 0; p < ulen;) {
         size_t n = ulen - p < block_max ? ulen - p : block_max;
-        int c = p_compress((const char*)src + p, (char*)dst + o + 4, (int)n, p_bound((int)n));
+        int c = stream ? p_continue(stream, (const char*)src + p, (char*)dst + o + 4, (int)n, p_bound((int)n), 1)
+                       : p_compress((const char*)src + p, (char*)dst + o + 4, (int)n, p_bound((int)n));
+        size_t bl;
         if (c <= 0 || (size_t)c >= n) { /* stored block */
             st32(dst + o, (uint32_t)n | 0x80000000u);
             memcpy(dst + o + 4, src + p, n);
-            o += 4 + n;
+            bl = n;
         } else {
             st32(dst + o, (uint32_t)c);
-            o += 4 + (size_t)c;
+            bl = (size_t)c;
         }
+        o += 4 + bl;
+        if (fflags & FF_BSUM) { st32(dst + o, xxh32(dst + o - bl, bl, 0)); o += 4; }
         p += n;
     }
+    if (stream) p_free(stream);
     st32(dst + o, 0);
-    return o + 4;
+    o += 4;
+    if (fflags & FF_CSUM) { st32(dst + o, xxh32(src, ulen, 0)); o += 4; }
+    return o;
 }
 
 /* Serialize chunks data[ends[i-1]..ends[i]) into one xorb chunk stream.  policy: 0 none, 1 lz4, 2 bg4-lz4;
  * a chunk whose frame is not smaller than the raw bytes is stored with scheme 0 (what xet-core does).
- * block_max: see lz4_frame_encode.  out must hold n*8 + len + n*32 + len/200 bytes.  Returns blob size. */
+ * block_max, fflags: see lz4_frame_encode (with fflags != 0 the framed form is kept even if it is not smaller).
+ * out must hold n*8 + len + n*32 + len/200 bytes.  Returns blob size. */
 OZ_API int64_t oz_build_xorb(const uint8_t* data, const uint64_t* ends, size_t n, int policy,
-                             size_t block_max, uint8_t* out, size_t out_cap) {
+                             size_t block_max, int fflags, uint8_t* out, size_t out_cap) {
     pthread_once(&lz4_once, lz4_load);
     if (policy && (!p_compress || !p_bound)) return OZ_ERR_NOLZ4;
     size_t o = 0, start = 0;
@@ -704,8 +731,8 @@ OZ_API int64_t oz_build_xorb(const uint8_t* data, const uint64_t* ends, size_t n
                 }
                 in = grp;
             }
-            size_t f = lz4_frame_encode(in, ul, frm, block_max);
-            if (f < ul) { cl = f; scheme = policy; }
+            size_t f = lz4_frame_encode(in, ul, frm, block_max, fflags);
+            if (f < ul || fflags) { cl = f; scheme = policy; }
         }
         if (o + 8 + cl > out_cap) { free(grp); free(frm); return OZ_ERR_CAPACITY; }
         uint8_t* h = out + o;

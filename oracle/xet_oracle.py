@@ -69,7 +69,7 @@ def lib():
         L.oz_hash_chunks_mt.argtypes = [u8p, u64p, C.c_size_t, u8p, C.c_int]
         L.oz_verify_xorbs_mt.argtypes = [C.c_void_p, C.c_void_p, u8p, C.c_size_t, C.c_void_p, u8p, u8p, C.c_int]
         L.oz_verify_xorbs_mt.restype = C.c_int64
-        L.oz_build_xorb.argtypes = [u8p, u64p, C.c_size_t, C.c_int, C.c_size_t, u8p, C.c_size_t]
+        L.oz_build_xorb.argtypes = [u8p, u64p, C.c_size_t, C.c_int, C.c_size_t, C.c_int, u8p, C.c_size_t]
         L.oz_build_xorb.restype = C.c_int64
         _lib = L
     return _lib
@@ -236,13 +236,16 @@ XORB_MAX_BYTES = 64 * 1024 * 1024
 XORB_MAX_CHUNKS = 8192
 
 
-def build_xorb(data, ends, policy: int, block_max: int = 0) -> bytes:
+FF_CSIZE, FF_BSUM, FF_CSUM, FF_LINKED = 1, 2, 4, 8
+
+
+def build_xorb(data, ends, policy: int, block_max: int = 0, fflags: int = 0) -> bytes:
     """Serialize chunks of `data` cut at `ends` into one xorb chunk stream (policy 0 none, 1 lz4, 2 bg4)."""
     d = _u8(data)
     e = np.ascontiguousarray(ends, dtype=np.uint64)
-    cap = d.size + e.size * 64 + d.size // 100 + 1024
+    cap = d.size + e.size * 96 + d.size // 50 + 4096
     out = np.empty(cap, np.uint8)
-    r = lib().oz_build_xorb(_p(d), _p(e), e.size, policy, block_max, _p(out), cap)
+    r = lib().oz_build_xorb(_p(d), _p(e), e.size, policy, block_max, fflags, _p(out), cap)
     if r < 0:
         raise OracleError(int(r))
     return out[:r].tobytes()
@@ -269,7 +272,7 @@ class SynthXorb:
     ulen_total: int
 
 
-def make_xorbs(data, policy: int, threads: int = 1, block_max: int = 0):
+def make_xorbs(data, policy: int, threads: int = 1, block_max: int = 0, fflags: int = 0):
     """CDC-chunk `data`, hash, and pack into xorbs.  -> (list[SynthXorb], ends u64, chunk_hashes (n,32))."""
     d = _u8(data)
     ends = cdc(d)
@@ -280,7 +283,7 @@ def make_xorbs(data, policy: int, threads: int = 1, block_max: int = 0):
     for lo, hi in split_into_xorbs(ends):
         b0 = int(off[lo])
         rel = (ends[lo:hi] - np.uint64(b0)).astype(np.uint64)
-        blob = build_xorb(d[b0:int(ends[hi - 1])], rel, policy, block_max)
+        blob = build_xorb(d[b0:int(ends[hi - 1])], rel, policy, block_max, fflags)
         xs.append(SynthXorb(blob, merkle_root(hashes[lo:hi], lens[lo:hi]), hi - lo, int(ends[hi - 1]) - b0))
     return xs, ends, hashes
 

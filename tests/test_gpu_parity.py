@@ -124,6 +124,30 @@ def test_synthetic_roundtrip(ctx, oracle, kind, policy, nbytes, block_max):
     assert res.verdict[0] == 1 and (res.chunk_hashes == hashes).all() and res.bytes_verified == nbytes
 
 
+@pytest.mark.parametrize("fflags", [1, 2, 4, 8, 9, 15])
+@pytest.mark.parametrize("block_max", [0, 65536, 4096])
+def test_frame_variants(ctx, oracle, fflags, block_max):
+    """Parts of the LZ4 frame format xet-core does not emit but a decoder must accept: content-size
+    field, block and content checksums (skipped), linked blocks whose matches reach into earlier blocks, many small
+    blocks, stored blocks."""
+    for kind, policy in (("text", 1), ("bf16", 2), ("rand", 1)):
+        data = getattr(oracle, GENS[kind])(500_001, fflags)
+        xs, _, hashes = oracle.make_xorbs(data, policy, block_max=block_max, fflags=fflags)
+        x = xs[0]
+        assert z.XorbReader(x.blob, ctx).extract_chunk_range(0, x.n_chunks) == data.tobytes()
+        res = z.verify_xorbs([x.blob], [x.expected], want_chunk_hashes=True, ctx=ctx)
+        assert res.ok and (res.chunk_hashes == hashes).all()
+        # a wrong content-size field / a cut frame must give the oracle's verdict
+        if fflags & 1:
+            idx = oracle.xorb_index(x.blob)
+            bad = bytearray(x.blob)
+            bad[int(idx.hdr_off[1]) + 8 + 6] ^= 1          # low byte of chunk 1's content size
+            bad = bytes(bad)
+            got = z.verify_xorbs([bad], [x.expected], ctx=ctx)
+            want, _, _ = oracle.verify_xorbs([bad], [x.expected])
+            assert got.verdict[0] == want[0] and want[0] < 0
+
+
 def test_special_streams(ctx, oracle):
     """Long matches (zeros, period-3, period-40), a one-byte file, an empty xorb list, an empty blob."""
     cases = [np.zeros(300_000, np.uint8), np.tile(np.frombuffer(b"abc", np.uint8), 100_000),

@@ -116,6 +116,16 @@ def test_builder_roundtrip(oracle):
             assert v[0] == 1 and nb == data.size
 
 
+def test_frame_variants(oracle):
+    """Optional LZ4 frame features (content size, checksums, linked and small blocks) round-trip through the oracle."""
+    for kind, policy in ((oracle.synth_zipf_text, 1), (oracle.synth_bf16, 2)):
+        data = kind(400_001, 9)
+        for ff in (1, 2, 4, 8, 15):
+            for bm in (0, 4096):
+                xs, _, _ = oracle.make_xorbs(data, policy, block_max=bm, fflags=ff)
+                assert oracle.extract_chunk_range(xs[0].blob, 0, xs[0].n_chunks) == data.tobytes()
+
+
 def test_corruption_detected(oracle, vectors):
     rec = next(r for r in vectors["real_xorbs"] if r["name"] == "xorb_text")
     stream, raw = read_golden_xorb(rec)

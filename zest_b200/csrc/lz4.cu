@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
         uint32_t wv0 = 0, wv1 = 0, wv2 = 0, wip = 0xffffffffu;  // raw words of the 8-byte window at position wip
 #pragma unroll 1
         for (int step = 0; step < kSeqCap; step++) {
-            const bool act = !finished && state != ST_IDLE && state != ST_EXHAUSTED;
+            const bool act = !finished && state != ST_IDLE && state != ST_EXHAUSTED && cnt < (uint32_t)kSeqCap;
             if (!__any_sync(0xffffffffu, act)) break;
             if (!act) continue;
             bool handled = false;
@@ -275,18 +275,30 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                 }
                 const uint32_t sh0 = (uint32_t)(a & 3) * 8;
                 const uint32_t lo = __funnelshift_r(wv0, wv1, sh0), hi = __funnelshift_r(wv1, wv2, sh0);
+                const uint64_t w64 = ((uint64_t)hi << 32) | lo;
                 const uint32_t tok = lo & 0xffu;
                 const uint32_t lit = tok >> 4, mln = tok & 15u;
                 if (lit != 15u && mln != 15u) {
-                    const uint32_t nip = ip + 3 + lit;
+                    // A second sequence that lies wholly inside the same 8-byte window (literal runs of 0-2 bytes are
+                    // the common case on both text and byte-grouped bf16) is taken in the same step: one load round
+                    // trip then yields two records.
+                    const uint32_t k1 = 3 + lit;
+                    uint32_t lit2 = 0, mln2 = 0, off2 = 0;
+                    bool two = false;
+                    if (k1 <= 5 && cnt + 2 <= (uint32_t)kSeqCap && ulen - op >= 72) {
+                        const uint32_t r = (uint32_t)(w64 >> (8 * k1));
+                        lit2 = (r >> 4) & 15u; mln2 = r & 15u;
+                        if (lit2 + k1 <= 5 && mln2 != 15u) {
+                            two = true;
+                            off2 = (uint32_t)(w64 >> (8 * (k1 + 1 + lit2))) & 0xffffu;
+                        }
+                    }
+                    const uint32_t nip = ip + k1 + (two ? 3 + lit2 : 0u);
                     const uint32_t* nw = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(src + nip) & ~(uintptr_t)3);
                     const uint32_t n0 = __ldg(nw), n1 = __ldg(nw + 1), n2 = __ldg(nw + 2);
                     uint32_t off;
-                    if (lit <= 5) {
-                        const uint32_t sh = 8 + 8 * lit;
-                        off = (sh < 32 ? __funnelshift_r(lo, hi, sh) : (hi >> (sh - 32))) & 0xffffu;
-                    } else
-                        off = rd8(src + ip + 1 + lit) | (rd8(src + ip + 2 + lit) << 8);
+                    if (lit <= 5) off = (uint32_t)(w64 >> (8 + 8 * lit)) & 0xffffu;
+                    else off = rd8(src + ip + 1 + lit) | (rd8(src + ip + 2 + lit) << 8);
                     const uint32_t vop = op + lit, ml = mln + 4;
                     if (off == 0 || off > vop - win_lo) { err = E_LZ4_BLOCK; finished = true; }
                     else {
@@ -295,8 +307,18 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                         pmask |= 1u << cnt;
                         cnt++;
                         op = vop + ml;
-                        ip = nip;
-                        wv0 = n0; wv1 = n1; wv2 = n2; wip = nip;
+                        if (two) {
+                            const uint32_t vop2 = op + lit2, ml2 = mln2 + 4;
+                            if (off2 == 0 || off2 > vop2 - win_lo) { err = E_LZ4_BLOCK; finished = true; }
+                            else {
+                                Seq e2{ip + k1 + 1, op, lit2 | (ml2 << 16), off2};
+                                ws.rec[cnt * 32 + (lane ^ cnt)] = e2;
+                                pmask |= 1u << cnt;
+                                cnt++;
+                                op = vop2 + ml2;
+                            }
+                        }
+                        if (!finished) { ip = nip; wv0 = n0; wv1 = n1; wv2 = n2; wip = nip; }
                     }
                     handled = true;
                 }

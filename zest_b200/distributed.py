@@ -31,6 +31,11 @@ def _dev():
         else torch.device("cpu")
 
 
+def shutdown():
+    if dist.is_initialized():
+        dist.destroy_process_group()
+
+
 def barrier():
     if dist.is_initialized():
         dist.barrier()
