@@ -342,7 +342,8 @@ def main():
                 "blake3_alu": {"compressions": int(compressions), "int_ops": int(int_ops),
                                "achieved_Tops": round(int_ops / stages["blake3_hash"] / 1e12, 3),
                                "peak_Tops": round(alu_peak_tops, 3), "frac": round(int_ops / stages["blake3_hash"] / 1e12 / alu_peak_tops, 4),
-                               "peak_source": f"148 SMs x 64 int lanes/clk x {sm_mhz:.0f} MHz observed"}}
+                               "peak_source": f"148 SMs x 64 int lanes/clk x {sm_mhz:.0f} MHz observed (the ALU pipe alone; the kernel "
+                                              "issues its adds as IMAD on the FMA pipe, so frac can exceed 1)"}}
     cpu = None
     if not args.no_cpu:
         v, best, reps = cpu_arm(blobs, expected, total, cores)

@@ -298,6 +298,8 @@ HashLayout hash_layout(uint64_t data_bytes, size_t n, int group) {
 }  // namespace
 
 int hash_pick_group(uint64_t data_bytes) {
+    static const int forced = []() { const char* e = getenv("ZEST_B3_GROUP"); int g = e ? atoi(e) : 0; return (g == 1 || g == 2 || g == 4 || g == 8) ? g : 0; }();
+    if (forced) return forced;  // tuning knob
     // keep >= ~57K threads (148 SMs x 12 warps) busy; beyond that fold more leaves per thread
     const uint64_t want = 148ull * 32 * 12;
     for (int g = 8; g > 1; g >>= 1)

@@ -192,6 +192,97 @@ __device__ __forceinline__ void warp_regroup(uint8_t* out, const uint8_t* tmp, u
     }
 }
 
+// ---- execute steps.  A 32-lane step covers two slots x 16 records (slot = base + lane / 16, record = lane % 16); NP = 2
+// issues two such steps back to back so the loads of four slots are in flight together, NP = 1 is used when the
+// second pair of slots is empty (small batches run with 1-2 slots per warp).
+
+// Pass 1: every literal run, and every match whose source lies wholly before this round's output.
+template <int NP>
+__device__ __forceinline__ void exec_pass1(WarpShared& ws, uint32_t it, uint32_t lane) {
+    const uint32_t half = lane >> 4, s = lane & 15;
+    Seq e[NP];
+    uint32_t lit[NP], ml[NP], n[NP], k[NP], c[NP], x[NP][4], y[NP][4];
+    const uint8_t* sp[NP];
+    uint8_t* dp[NP];
+    bool old[NP];
+#pragma unroll
+    for (int q = 0; q < NP; q++) {
+        c[q] = 2 * it + half + 2 * q;
+        e[q] = Seq{0, 0, 0, 0};
+        if (s < ws.cnt[c[q]]) e[q] = ws.rec[s * 32 + (c[q] ^ s)];
+        lit[q] = e[q].lens & 0xffffu; ml[q] = e[q].lens >> 16;
+        sp[q] = reinterpret_cast<const uint8_t*>(ws.src[c[q]]) + e[q].lit_src;
+        dp[q] = reinterpret_cast<uint8_t*>(ws.lz[c[q]]) + e[q].dst;
+        n[q] = lit[q] <= kShort ? lit[q] : 0u;
+        // "old" match: short, and its source ends at or before the first byte this round produces for the slot
+        old[q] = ml[q] != 0 && ml[q] <= kShort && e[q].dst + lit[q] - e[q].off + ml[q] <= ws.w0[c[q]];
+        k[q] = old[q] ? ml[q] : 0u;
+    }
+#pragma unroll
+    for (int q = 0; q < NP; q++) load16<true>(sp[q], n[q], x[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) load16<false>(dp[q] + lit[q] - e[q].off, k[q], y[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) store16(dp[q], n[q], x[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) store16(dp[q] + lit[q], k[q], y[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) {
+        if (old[q]) atomicAnd(&ws.pend[c[q]], ~(1u << s));
+        uint32_t lm = __ballot_sync(0xffffffffu, lit[q] > kShort);  // long literal runs: whole-warp copies
+        while (lm) {
+            int l = __ffs(lm) - 1;
+            lm &= lm - 1;
+            uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dp[q]), l));
+            const uint8_t* g = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(sp[q]), l));
+            warp_copy<false>(d, g, __shfl_sync(0xffffffffu, lit[q], l), lane);
+        }
+    }
+}
+
+// Pass 2, one round: matches that read this round's own output and whose source now lies below their slot's frontier.
+template <int NP>
+__device__ __forceinline__ void exec_pass2(WarpShared& ws, uint32_t it, uint32_t lane) {
+    const uint32_t half = lane >> 4, s = lane & 15;
+    Seq e[NP];
+    uint32_t ml[NP], md[NP], c[NP], x[NP][4];
+    uint8_t* dp[NP];
+    bool pd[NP], fs[NP], go[NP], fast[NP];
+#pragma unroll
+    for (int q = 0; q < NP; q++) {
+        c[q] = 2 * it + half + 2 * q;
+        e[q] = Seq{0, 0, 0, 0};
+        pd[q] = (ws.pend[c[q]] >> s) & 1;
+        if (pd[q]) e[q] = ws.rec[s * 32 + (c[q] ^ s)];
+        ml[q] = e[q].lens >> 16;
+        md[q] = e[q].dst + (e[q].lens & 0xffffu);
+        fs[q] = pd[q] && s == ws.first[c[q]];
+        dp[q] = reinterpret_cast<uint8_t*>(ws.lz[c[q]]) + md[q];
+        // long matches run when they are first in their slot, with the whole warp
+        uint32_t lm = __ballot_sync(0xffffffffu, fs[q] && ml[q] > kShort);
+        while (lm) {
+            int l = __ffs(lm) - 1;
+            lm &= lm - 1;
+            uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dp[q]), l));
+            warp_match(d, __shfl_sync(0xffffffffu, e[q].off, l), __shfl_sync(0xffffffffu, ml[q], l), lane);
+        }
+        go[q] = pd[q] && ml[q] <= kShort && (fs[q] || md[q] - e[q].off + ml[q] <= ws.frontier[c[q]]);
+        fast[q] = go[q] && e[q].off >= ml[q];
+    }
+#pragma unroll
+    for (int q = 0; q < NP; q++) load16<false>(dp[q] - e[q].off, fast[q] ? ml[q] : 0u, x[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) store16(dp[q], fast[q] ? ml[q] : 0u, x[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) {
+        if (go[q] && !fast[q]) {  // self-overlapping short match: byte-serial
+            const uint8_t* g = dp[q] - e[q].off;
+            for (uint32_t b = 0; b < ml[q]; b++) dp[q][b] = g[b];
+        }
+        if (go[q] || (fs[q] && ml[q] > kShort)) atomicAnd(&ws.pend[c[q]], ~(1u << s));
+    }
+}
+
 __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* __restrict__ comp,
                                                                  const ChunkDesc* __restrict__ chunks, uint32_t n_chunks,
                                                                  uint8_t* out, uint8_t* tmp, int32_t* __restrict__ status,
@@ -468,54 +559,13 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
         const uint32_t have = __ballot_sync(0xffffffffu, cnt > 0);  // slots with records this round
 
         // ---- execute, pass 1: every literal run, and every match whose source lies wholly before this round's
-        // output (no dependence on anything written this round: ~91 % of matches on text, ~98 % on byte-grouped
-        // bf16).  A 32-lane step covers two slots x 16 records; two steps are issued back to back so the loads of four
-        // slots (literal + match source each) are in flight together.
-        const uint32_t half = lane >> 4, s = lane & 15;
+        // output (no dependence on anything written this round: ~91 % of matches on text, ~98 % on byte-grouped bf16)
 #pragma unroll 1
         for (uint32_t it = 0; it < 16; it += 2) {
-            if (((have >> (2 * it)) & 0xfu) == 0) continue;
-            const uint32_t cA = 2 * it + half, cB = cA + 2;
-            Seq eA{0, 0, 0, 0}, eB{0, 0, 0, 0};
-            if (s < ws.cnt[cA]) eA = ws.rec[s * 32 + (cA ^ s)];
-            if (s < ws.cnt[cB]) eB = ws.rec[s * 32 + (cB ^ s)];
-            const uint32_t litA = eA.lens & 0xffffu, litB = eB.lens & 0xffffu;
-            const uint32_t mlA = eA.lens >> 16, mlB = eB.lens >> 16;
-            const uint8_t* sA = reinterpret_cast<const uint8_t*>(ws.src[cA]) + eA.lit_src;
-            const uint8_t* sB = reinterpret_cast<const uint8_t*>(ws.src[cB]) + eB.lit_src;
-            uint8_t* dA = reinterpret_cast<uint8_t*>(ws.lz[cA]) + eA.dst;
-            uint8_t* dB = reinterpret_cast<uint8_t*>(ws.lz[cB]) + eB.dst;
-            const uint32_t nA = litA <= kShort ? litA : 0u, nB = litB <= kShort ? litB : 0u;
-            // "old" match: short, and its source ends at or before the first byte this round produces for the slot
-            const bool oldA = mlA != 0 && mlA <= kShort && eA.dst + litA - eA.off + mlA <= ws.w0[cA];
-            const bool oldB = mlB != 0 && mlB <= kShort && eB.dst + litB - eB.off + mlB <= ws.w0[cB];
-            const uint32_t kA = oldA ? mlA : 0u, kB = oldB ? mlB : 0u;
-            uint32_t xA[4], xB[4], yA[4], yB[4];
-            load16<true>(sA, nA, xA);
-            load16<true>(sB, nB, xB);
-            load16<false>(dA + litA - eA.off, kA, yA);
-            load16<false>(dB + litB - eB.off, kB, yB);
-            store16(dA, nA, xA);
-            store16(dB, nB, xB);
-            store16(dA + litA, kA, yA);
-            store16(dB + litB, kB, yB);
-            if (oldA) atomicAnd(&ws.pend[cA], ~(1u << s));
-            if (oldB) atomicAnd(&ws.pend[cB], ~(1u << s));
-            uint32_t lA = __ballot_sync(0xffffffffu, litA > kShort), lB = __ballot_sync(0xffffffffu, litB > kShort);
-            while (lA) {
-                int l = __ffs(lA) - 1;
-                lA &= lA - 1;
-                uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dA), l));
-                const uint8_t* q = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(sA), l));
-                warp_copy<false>(d, q, __shfl_sync(0xffffffffu, litA, l), lane);
-            }
-            while (lB) {
-                int l = __ffs(lB) - 1;
-                lB &= lB - 1;
-                uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dB), l));
-                const uint8_t* q = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(sB), l));
-                warp_copy<false>(d, q, __shfl_sync(0xffffffffu, litB, l), lane);
-            }
+            const uint32_t m4 = (have >> (2 * it)) & 0xfu;
+            if (m4 == 0) continue;
+            if (m4 >> 2) exec_pass1<2>(ws, it, lane);
+            else exec_pass1<1>(ws, it, lane);
         }
         __syncwarp();
         ZG_T(t_p1);
@@ -539,43 +589,10 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
 #endif
 #pragma unroll 1
             for (uint32_t it = 0; it < 16; it += 2) {
-                if (((anyp >> (2 * it)) & 0xfu) == 0) continue;
-                const uint32_t cA = 2 * it + half, cB = cA + 2;
-                Seq eA{0, 0, 0, 0}, eB{0, 0, 0, 0};
-                const bool pA = (ws.pend[cA] >> s) & 1, pB = (ws.pend[cB] >> s) & 1;
-                if (pA) eA = ws.rec[s * 32 + (cA ^ s)];
-                if (pB) eB = ws.rec[s * 32 + (cB ^ s)];
-                const uint32_t mlA = eA.lens >> 16, mlB = eB.lens >> 16;
-                const uint32_t mdA = eA.dst + (eA.lens & 0xffffu), mdB = eB.dst + (eB.lens & 0xffffu);
-                const bool fA = pA && s == ws.first[cA], fB = pB && s == ws.first[cB];
-                uint8_t* dA = reinterpret_cast<uint8_t*>(ws.lz[cA]) + mdA;
-                uint8_t* dB = reinterpret_cast<uint8_t*>(ws.lz[cB]) + mdB;
-                // long matches run when they are first in their slot, with the whole warp
-                uint32_t longA = __ballot_sync(0xffffffffu, fA && mlA > kShort), longB = __ballot_sync(0xffffffffu, fB && mlB > kShort);
-                while (longA) {
-                    int l = __ffs(longA) - 1;
-                    longA &= longA - 1;
-                    uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dA), l));
-                    warp_match(d, __shfl_sync(0xffffffffu, eA.off, l), __shfl_sync(0xffffffffu, mlA, l), lane);
-                }
-                while (longB) {
-                    int l = __ffs(longB) - 1;
-                    longB &= longB - 1;
-                    uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dB), l));
-                    warp_match(d, __shfl_sync(0xffffffffu, eB.off, l), __shfl_sync(0xffffffffu, mlB, l), lane);
-                }
-                const bool goA = pA && mlA <= kShort && (fA || mdA - eA.off + mlA <= ws.frontier[cA]);
-                const bool goB = pB && mlB <= kShort && (fB || mdB - eB.off + mlB <= ws.frontier[cB]);
-                const bool fastA = goA && eA.off >= mlA, fastB = goB && eB.off >= mlB;
-                uint32_t xA[4], xB[4];
-                load16<false>(dA - eA.off, fastA ? mlA : 0u, xA);
-                load16<false>(dB - eB.off, fastB ? mlB : 0u, xB);
-                store16(dA, fastA ? mlA : 0u, xA);
-                store16(dB, fastB ? mlB : 0u, xB);
-                if (goA && !fastA) { const uint8_t* q = dA - eA.off; for (uint32_t b = 0; b < mlA; b++) dA[b] = q[b]; }
-                if (goB && !fastB) { const uint8_t* q = dB - eB.off; for (uint32_t b = 0; b < mlB; b++) dB[b] = q[b]; }
-                if (goA || (fA && mlA > kShort)) atomicAnd(&ws.pend[cA], ~(1u << s));
-                if (goB || (fB && mlB > kShort)) atomicAnd(&ws.pend[cB], ~(1u << s));
+                const uint32_t m4 = (anyp >> (2 * it)) & 0xfu;
+                if (m4 == 0) continue;
+                if (m4 >> 2) exec_pass2<2>(ws, it, lane);
+                else exec_pass2<1>(ws, it, lane);
             }
             __syncwarp();
         }
@@ -643,10 +660,11 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     // Slots (chunks in flight) per warp: few when the batch is small, so that every SM gets many warps (the token walk
     // and the copy rounds are latency chains; only other warps hide them); up to 32 for large batches, where the
     // serial token walk is then spread over all lanes.  Chunks are handed out longest-first through the ticket
-    // counter, and the launch keeps about half as many slots as chunks: a slot that finishes a long chunk picks up
-    // a short one, so the tail stays balanced.  Measured on B200 (profiles/): 8.5k text chunks -> 2 slots, 15.7k
+    // counter, and for batches larger than the machine the launch keeps about half as many slots as chunks: a slot
+    // that finishes a long chunk picks up a short one, so the tail stays balanced.  Measured on B200 (profiles/): 8.5k text chunks -> 2 slots, 15.7k
     // bf16 chunks -> 4 slots.  ZEST_LZ4_SLOTS / ZEST_LZ4_WARPS / ZEST_LZ4_OVERSUB override (tuning knobs).
-    size_t want_warps = 148 * 16, max_warps = 148 * 24, oversub = 2;
+    size_t want_warps = 148 * 16, max_warps = 148 * 24;
+    size_t oversub = n > max_warps ? 2 : 1;  // a batch that fits the machine at one chunk per slot runs at single-chunk latency
     if (const char* e = getenv("ZEST_LZ4_WARPS")) { long v = atol(e); if (v > 0) want_warps = max_warps = (size_t)v; }
     if (const char* e = getenv("ZEST_LZ4_OVERSUB")) { long v = atol(e); if (v > 0) oversub = (size_t)v; }
     uint32_t slots = (uint32_t)((n + want_warps * oversub - 1) / (want_warps * oversub));
