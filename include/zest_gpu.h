@@ -53,7 +53,7 @@ typedef struct zg_ctx zg_ctx;
 
 typedef struct zg_opts {
     uint32_t struct_size; /* sizeof(zg_opts), for forward compatibility                         */
-    uint32_t n_lanes;     /* concurrent calls served at once (streams); 0 = default (4)        */
+    uint32_t n_lanes;     /* concurrent calls served at once (streams); 0 = default (8)        */
     uint64_t reserved[3];
 } zg_opts;
 
@@ -83,6 +83,15 @@ ZG_API int zg_hex_to_hash(const char* hex, uint8_t out[32]);
  * hdr_off[i] = byte offset of chunk i's header.  Returns ZG_ERR_CAPACITY if the blob has more than cap chunks. */
 ZG_API int zg_xorb_index(const uint8_t* blob, size_t len, uint32_t cap, uint32_t* n_chunks, uint64_t* hdr_off,
                   uint32_t* clen, uint32_t* ulen, uint8_t* scheme, uint64_t* total_ulen);
+
+/* The "XETBLOB" footer xet-core appends to a stored xorb: xorb hash, every chunk hash, cumulative
+ * compressed / uncompressed boundaries, section offsets, and the trailing length word.  With the chunk hashes and root
+ * that zg_verify_xorbs / zg_cdc_hash return, this completes a XorbCache-format blob on the seed path
+ * (XorbCache.put, src/swarm.zig:57-148).  out receives zg_xorb_footer_bytes(n) bytes to append
+ * after the chunk stream. */
+ZG_API size_t zg_xorb_footer_bytes(size_t n_chunks);
+ZG_API int zg_xorb_footer(const uint8_t xorb_hash[32], const uint8_t* chunk_hashes, const uint32_t* clen,
+                          const uint32_t* ulen, size_t n, uint8_t* out, size_t out_cap, size_t* out_len);
 
 /* Size of extractChunkRange(start, end)'s result, so the caller can allocate. */
 ZG_API int zg_chunk_range_size(const uint8_t* blob, size_t len, uint32_t start, uint32_t end, uint64_t* out_len);

@@ -107,6 +107,15 @@ def test_extract_real_xorbs(ctx, oracle, vectors, name):
     assert ei.value.code == -9
 
 
+@pytest.mark.parametrize("name", ["xorb_bf16", "xorb_text", "xorb_rand", "xorb_mixed_auto", "xorb_tiny"])
+def test_seal_xorb_reproduces_xet_core_file(ctx, vectors, name):
+    """Seed path: chunk stream -> GPU chunk hashes + Merkle root -> XETBLOB footer == the file xet-core stored."""
+    rec = next(r for r in vectors["real_xorbs"] if r["name"] == name)
+    stream, raw = read_golden_xorb(rec)
+    blob, root = z.seal_xorb(stream, ctx)
+    assert blob == raw and z.hash_to_hex(root) == rec["xorb_hash"]
+
+
 GENS = {"text": "synth_zipf_text", "bf16": "synth_bf16", "rand": "synth_random"}
 
 
@@ -202,6 +211,38 @@ def test_many_xorbs_batch(ctx, oracle):
     want_v, want_roots, want_bytes = oracle.verify_xorbs(blobs, expected, threads=8)
     assert list(got.verdict) == list(want_v) and got.verdict[7] <= 0
     assert (got.roots[want_v >= 0] == want_roots[want_v >= 0]).all()
+
+
+def test_concurrent_callers(ctx, oracle, vectors):
+    """zest fans out up to 128 concurrent tasks per batch (src/parallel_download.zig:117,174-182), each calling
+    extractChunkRange on its own term: many host threads on one context must all get oracle-exact bytes."""
+    import threading
+    items = []
+    for name in ("xorb_text", "xorb_bf16", "xorb_mixed_auto", "xorb_rand"):
+        rec = next(r for r in vectors["real_xorbs"] if r["name"] == name)
+        stream, raw = read_golden_xorb(rec)
+        _, _, xh = footer_chunk_hashes(raw)
+        n = rec["n_chunks"]
+        for (s, e) in [(0, n), (1, n), (0, n - 1), (n // 2, n)]:
+            items.append((stream, s, e, oracle.extract_chunk_range(stream, s, e), xh))
+    errors = []
+
+    def worker(k):
+        try:
+            for rep in range(6):
+                stream, s, e, want, xh = items[(k + rep) % len(items)]
+                assert z.XorbReader(stream, ctx).extract_chunk_range(s, e) == want
+                if rep % 3 == 0:
+                    assert z.verify_xorbs([stream], [xh], ctx=ctx).ok
+        except Exception as ex:  # noqa: BLE001
+            errors.append(repr(ex))
+
+    ts = [threading.Thread(target=worker, args=(k,)) for k in range(32)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errors, errors[:3]
 
 
 # ------------------------------------------------------------------------------------------------ CDC

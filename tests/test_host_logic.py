@@ -89,3 +89,14 @@ def test_partition_xorbs():
         assert sorted(i for p in parts for i in p) == list(range(len(sizes)))
         loads = [sum(sizes[i] for i in p) for p in parts]
         assert max(loads) - min(loads) <= max(sizes)
+
+
+@pytest.mark.parametrize("name", ["xorb_bf16", "xorb_text", "xorb_rand", "xorb_mixed_auto", "xorb_tiny"])
+def test_xetblob_footer_matches_xet_core(vectors, name):
+    """zg_xorb_footer reproduces, byte for byte, the footer xet-core wrote for the golden xorbs."""
+    from conftest import footer_chunk_hashes
+    rec = next(r for r in vectors["real_xorbs"] if r["name"] == name)
+    stream, raw = read_golden_xorb(rec)
+    hashes, _, xorb_hash = footer_chunk_hashes(raw)
+    ix = z.xorb_index(stream)
+    assert z.xorb_footer(xorb_hash, hashes, ix.clen, ix.ulen) == raw[len(stream):]

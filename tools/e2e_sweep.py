@@ -21,8 +21,8 @@ dt = (time.perf_counter() - t0) / K
 print(f"{dt*1e3:8.2f} ms  {total/dt/1e9:7.1f} GB/s uncompressed  {p/dt/1e9:6.1f} GB/s H2D")
 ''' % ROOT
 wl, nbytes = sys.argv[1], sys.argv[2]
-for mb in (64, 128, 256, 1024):
-    for lanes in (1, 2, 4):
+for mb in [int(x) for x in (sys.argv[3] if len(sys.argv) > 3 else '64,128,256,1024').split(',')]:
+    for lanes in [int(x) for x in (sys.argv[4] if len(sys.argv) > 4 else '1,2,4').split(',')]:
         env = dict(os.environ, ZEST_VERIFY_SUBBATCH_MB=str(mb), ZEST_VERIFY_LANES=str(lanes))
         out = subprocess.run([sys.executable, "-c", CODE, wl, nbytes], env=env, capture_output=True, text=True)
         print(f"subbatch={mb:5d} MB lanes={lanes}: {out.stdout.strip() or out.stderr.strip()[-300:]}", flush=True)

@@ -11,10 +11,10 @@ from ._native import ZestGpuError, LIB_PATH, build  # noqa: F401
 from .context import Context, default_context  # noqa: F401
 from .hashing import (PLAIN_BLAKE3, blake3, chunk_hash, file_hash, hash_chunks, hash_to_hex, hex_to_hash,  # noqa: F401
                       merkle_root)
-from .xorb import XorbIndex, XorbReader, xorb_index  # noqa: F401
+from .xorb import XorbIndex, XorbReader, seal_xorb, xorb_footer, xorb_index  # noqa: F401
 from .verify import VerifyResult, partition_xorbs, verify_xorbs  # noqa: F401
 from .chunking import cdc, cdc_hash  # noqa: F401
 
-__all__ = ["Context", "default_context", "ZestGpuError", "XorbReader", "XorbIndex", "xorb_index", "verify_xorbs",
+__all__ = ["Context", "default_context", "ZestGpuError", "XorbReader", "XorbIndex", "xorb_index", "xorb_footer", "seal_xorb", "verify_xorbs",
            "VerifyResult", "partition_xorbs", "hash_chunks", "chunk_hash", "blake3", "merkle_root", "file_hash",
            "hash_to_hex", "hex_to_hash", "cdc", "cdc_hash", "PLAIN_BLAKE3", "build", "LIB_PATH"]

@@ -26,7 +26,7 @@ SYMBOLS = [
     "zg_hash_chunks", "zg_merkle_root", "zg_cdc", "zg_cdc_hash", "zg_dev_hash_scratch_bytes", "zg_dev_hash_chunks",
     "zg_dev_decode_scratch_bytes", "zg_dev_decode_chunks", "zg_dev_merkle_scratch_bytes", "zg_dev_merkle",
     "zg_dev_verify_scratch_bytes", "zg_dev_verify_xorbs", "zg_dev_cdc_scratch_bytes", "zg_dev_cdc", "zg_get_stats",
-    "zg_chunk_order", "zg_dev_hash_chunks_static",
+    "zg_chunk_order", "zg_dev_hash_chunks_static", "zg_xorb_footer_bytes", "zg_xorb_footer",
 ]
 
 
@@ -104,6 +104,9 @@ def lib() -> C.CDLL:
         L.zg_dev_cdc.argtypes = [vp, vp, u64, vp, u64, vp, vp, sz, vp]
         L.zg_get_stats.argtypes = [vp, C.POINTER(Stats)]
         L.zg_dev_hash_chunks_static.argtypes = [vp, u64, vp, vp, sz, vp, vp, vp]
+        L.zg_xorb_footer_bytes.argtypes = [sz]
+        L.zg_xorb_footer_bytes.restype = sz
+        L.zg_xorb_footer.argtypes = [vp, vp, vp, vp, sz, vp, sz, C.POINTER(sz)]
         L.zg_chunk_order.argtypes = [vp, sz]
         L.zg_chunk_order.restype = None
         _lib = L

@@ -198,7 +198,7 @@ int zg_init(int device, const zg_opts* opts, zg_ctx** out) {
     zg_ctx* c = new (std::nothrow) zg_ctx();
     if (!c) return fail(ZG_ERR_OOM, "out of host memory");
     c->device = device;
-    uint32_t nl = (opts && opts->struct_size >= 8 && opts->n_lanes) ? opts->n_lanes : 4;
+    uint32_t nl = (opts && opts->struct_size >= 8 && opts->n_lanes) ? opts->n_lanes : 8;
     if (nl > 64) nl = 64;
     c->lanes.resize(nl);
     for (auto& l : c->lanes) {
@@ -396,7 +396,7 @@ uint64_t sub_batch_bytes() {  // ZEST_VERIFY_SUBBATCH_MB: tuning knob
     return v;
 }
 int max_verify_lanes() {  // ZEST_VERIFY_LANES: tuning knob
-    static const int v = []() { const char* e = getenv("ZEST_VERIFY_LANES"); long m = e ? atol(e) : 0; return (int)(m > 0 && m < 4 ? m : 4); }();
+    static const int v = []() { const char* e = getenv("ZEST_VERIFY_LANES"); long m = e ? atol(e) : 0; return (int)(m > 0 && m < 8 ? m : 4); }();
     return v;
 }
 
@@ -414,10 +414,10 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
     // Up to four lanes: the copies of one sub-batch overlap the kernels of the others and the host walk of the next.
     // Several sub-batches in flight also matter for the decoder itself: one LZ4 chunk is a serial chain of a few
     // milliseconds, so a single ~128 MB sub-batch cannot fill the GPU; three or four of them on separate streams do.
-    constexpr int kMaxSlots = 4;
-    LaneGuard g0(ctx), g1(ctx, false), g2(ctx, false), g3(ctx, false);
+    constexpr int kMaxSlots = 8;
+    LaneGuard g0(ctx), g1(ctx, false), g2(ctx, false), g3(ctx, false), g4(ctx, false), g5(ctx, false), g6(ctx, false), g7(ctx, false);
     VerifySlot slots[kMaxSlots];
-    Lane* got[kMaxSlots] = {g0.l, g1.l, g2.l, g3.l};
+    Lane* got[kMaxSlots] = {g0.l, g1.l, g2.l, g3.l, g4.l, g5.l, g6.l, g7.l};
     int n_slots = 0;
     for (int i = 0; i < kMaxSlots && n_slots < max_verify_lanes(); i++)
         if (got[i]) slots[n_slots++].L = got[i];
@@ -822,6 +822,41 @@ int zg_dev_cdc(zg_ctx* ctx, const uint8_t* d_data, uint64_t len, uint64_t* d_end
     if (r) return r;
     CU(launch_cdc(d_data, len, d_ends, cap, d_n_out, d_scratch, scratch_bytes, static_cast<cudaStream_t>(stream)));
     ctx->kernels += 2;
+    return ZG_OK;
+}
+
+size_t zg_xorb_footer_bytes(size_t n_chunks) { return 96 + 40 * n_chunks; }
+
+int zg_xorb_footer(const uint8_t xorb_hash[32], const uint8_t* chunk_hashes, const uint32_t* clen, const uint32_t* ulen,
+                   size_t n, uint8_t* out, size_t out_cap, size_t* out_len) {
+    if (!xorb_hash || !out_len || (n && (!chunk_hashes || !clen || !ulen))) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    if (n > 0x7fffffffull) return fail(ZG_ERR_LIMIT, "too many chunks");
+    const size_t total = zg_xorb_footer_bytes(n);
+    *out_len = total;
+    if (total > out_cap || !out) return fail(ZG_ERR_CAPACITY, "footer needs %zu bytes, buffer holds %zu", total, out_cap);
+    const uint32_t info_len = (uint32_t)(total - 4);
+    auto put32 = [](uint8_t* p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); };
+    uint8_t* p = out;
+    memcpy(p, "XETBLOB", 7); p[7] = 1; p += 8;
+    memcpy(p, xorb_hash, 32); p += 32;
+    const uint32_t hashes_at = (uint32_t)(p - out);
+    memcpy(p, "XBLBHSH", 7); p[7] = 0; p += 8;
+    put32(p, (uint32_t)n); p += 4;
+    if (n) memcpy(p, chunk_hashes, 32 * n);
+    p += 32 * n;
+    const uint32_t bnd_at = (uint32_t)(p - out);
+    memcpy(p, "XBLBBND", 7); p[7] = 1; p += 8;
+    put32(p, (uint32_t)n); p += 4;
+    uint64_t c = 0, u = 0;
+    for (size_t i = 0; i < n; i++) { c += 8ull + clen[i]; if (c > 0xffffffffull) return fail(ZG_ERR_LIMIT, "xorb larger than 4 GiB"); put32(p + 4 * i, (uint32_t)c); }
+    p += 4 * n;
+    for (size_t i = 0; i < n; i++) { u += ulen[i]; if (u > 0xffffffffull) return fail(ZG_ERR_LIMIT, "xorb larger than 4 GiB"); put32(p + 4 * i, (uint32_t)u); }
+    p += 4 * n;
+    put32(p, (uint32_t)n); p += 4;
+    put32(p, info_len - hashes_at); p += 4;
+    put32(p, info_len - bnd_at); p += 4;
+    memset(p, 0, 16); p += 16;
+    put32(p, info_len); p += 4;
     return ZG_OK;
 }
 

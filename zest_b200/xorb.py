@@ -68,3 +68,31 @@ class XorbReader:
         return out[:got.value].tobytes()
 
     extractChunkRange = extract_chunk_range  # the reference's spelling
+
+
+def xorb_footer(xorb_hash, chunk_hashes, clen, ulen) -> bytes:
+    """The XETBLOB footer xet-core appends to a stored xorb (zg_xorb_footer)."""
+    h = _u8(xorb_hash)
+    ch = np.ascontiguousarray(chunk_hashes, dtype=np.uint8).reshape(-1, 32)
+    cl = np.ascontiguousarray(clen, dtype=np.uint32)
+    ul = np.ascontiguousarray(ulen, dtype=np.uint32)
+    n = cl.size
+    L = _native.lib()
+    out = np.empty(L.zg_xorb_footer_bytes(n), np.uint8)
+    got = C.c_size_t()
+    check(L.zg_xorb_footer(h.ctypes.data, ch.ctypes.data, cl.ctypes.data, ul.ctypes.data, n, out.ctypes.data, out.size,
+                           C.byref(got)))
+    return out[:got.value].tobytes()
+
+
+def seal_xorb(stream, ctx: Context | None = None) -> tuple[bytes, bytes]:
+    """Seed path: chunk stream -> (XorbCache-format blob = stream + XETBLOB footer, xorb hash).  The chunk hashes and
+    the Merkle root come from the GPU (verify_xorbs without an expected hash)."""
+    from .verify import verify_xorbs
+    b = _u8(stream)
+    ix = xorb_index(b)
+    res = verify_xorbs([b], None, want_chunk_hashes=True, ctx=ctx)
+    if res.verdict[0] < 0:
+        raise _native.ZestGpuError(int(res.verdict[0]), "chunk stream does not decode")
+    root = res.roots[0].tobytes()
+    return b.tobytes() + xorb_footer(root, res.chunk_hashes, ix.clen, ix.ulen), root
