@@ -24,7 +24,7 @@
  * file against every one of them.  Parity with zig-xet itself is by protocol equivalence ("unpinned by the
  * reference").
  *
- * Build: make -C oracle   ->  oracle/libxet_oracle.so   (gcc -O3 -march=native -pthread)
+ * Build: make -C oracle   ->  oracle/libxet_oracle.so   (gcc -O3 -march=x86-64-v3 -pthread)
  */
 #define _GNU_SOURCE
 #include <dlfcn.h>
@@ -141,6 +141,58 @@ static void b3_leaf(const uint32_t key[8], uint32_t base_flags, const uint8_t* p
     memcpy(out, cv, sizeof cv);
 }
 
+/* Eight full 1 KiB leaves at once (one leaf per SIMD lane, GCC vector extensions -> AVX2): the same compression,
+ * written over vectors.  This is only here so that the timed CPU arm is a fair stand-in for the reference's
+ * std.crypto BLAKE3 (which is SIMD too); results are identical to b3_leaf and the tests compare both paths. */
+typedef uint32_t v8u __attribute__((vector_size(32)));
+#define V8_ROTR(x, n) (((x) >> (n)) | ((x) << (32 - (n))))
+#define V8_G(a, b, c, d, x, y)             \
+    do {                                   \
+        v[a] = v[a] + v[b] + (x);          \
+        v[d] = V8_ROTR(v[d] ^ v[a], 16);   \
+        v[c] = v[c] + v[d];                \
+        v[b] = V8_ROTR(v[b] ^ v[c], 12);   \
+        v[a] = v[a] + v[b] + (y);          \
+        v[d] = V8_ROTR(v[d] ^ v[a], 8);    \
+        v[c] = v[c] + v[d];                \
+        v[b] = V8_ROTR(v[b] ^ v[c], 7);    \
+    } while (0)
+
+static void b3_leaves8(const uint32_t key[8], uint32_t base_flags, const uint8_t* p, uint64_t first_leaf,
+                       uint32_t out[8][8]) {
+    v8u cv[8];
+    for (int i = 0; i < 8; i++) cv[i] = (v8u){key[i], key[i], key[i], key[i], key[i], key[i], key[i], key[i]};
+    v8u ctr_lo, ctr_hi;
+    for (int j = 0; j < 8; j++) { ctr_lo[j] = (uint32_t)(first_leaf + j); ctr_hi[j] = (uint32_t)((first_leaf + j) >> 32); }
+    for (int b = 0; b < 16; b++) {
+        v8u m[16], t[16], v[16];
+        for (int i = 0; i < 16; i++)
+            for (int j = 0; j < 8; j++) m[i][j] = ld32(p + 1024 * j + 64 * b + 4 * i);
+        uint32_t fl = base_flags | (b == 0 ? B3_CHUNK_START : 0) | (b == 15 ? B3_CHUNK_END : 0);
+        for (int i = 0; i < 8; i++) v[i] = cv[i];
+        for (int i = 0; i < 4; i++) v[8 + i] = (v8u){B3_IV[i], B3_IV[i], B3_IV[i], B3_IV[i], B3_IV[i], B3_IV[i], B3_IV[i], B3_IV[i]};
+        v[12] = ctr_lo; v[13] = ctr_hi;
+        v[14] = (v8u){64, 64, 64, 64, 64, 64, 64, 64};
+        v[15] = (v8u){fl, fl, fl, fl, fl, fl, fl, fl};
+        for (int r = 0;; r++) {
+            V8_G(0, 4, 8, 12, m[0], m[1]);
+            V8_G(1, 5, 9, 13, m[2], m[3]);
+            V8_G(2, 6, 10, 14, m[4], m[5]);
+            V8_G(3, 7, 11, 15, m[6], m[7]);
+            V8_G(0, 5, 10, 15, m[8], m[9]);
+            V8_G(1, 6, 11, 12, m[10], m[11]);
+            V8_G(2, 7, 8, 13, m[12], m[13]);
+            V8_G(3, 4, 9, 14, m[14], m[15]);
+            if (r == 6) break;
+            for (int i = 0; i < 16; i++) t[i] = m[B3_PERM[i]];
+            for (int i = 0; i < 16; i++) m[i] = t[i];
+        }
+        for (int i = 0; i < 8; i++) cv[i] = v[i] ^ v[i + 8];
+    }
+    for (int j = 0; j < 8; j++)
+        for (int i = 0; i < 8; i++) out[j][i] = cv[i][j];
+}
+
 /* Full BLAKE3 of `len` bytes under `key` words and mode flags (0 = plain hash with IV as key).
  * The tree is reduced level by level, pairing neighbours and promoting an odd tail unchanged; SURVEY.md
  * A.2 records that this equals BLAKE3's left-full tree (checked against PyPI blake3 in tests). */
@@ -148,7 +200,10 @@ static void b3_hash(const uint32_t key[8], uint32_t base_flags, const uint8_t* p
                     uint8_t out[32]) {
     size_t nleaves = len == 0 ? 1 : (len + 1023) / 1024;
     uint32_t(*cvs)[8] = malloc(nleaves * sizeof *cvs);
-    for (size_t i = 0; i < nleaves; i++) {
+    size_t i0 = 0;
+    for (; i0 + 8 <= nleaves && (i0 + 8) * 1024 <= len && nleaves > 8; i0 += 8)  /* eight full leaves per pass */
+        b3_leaves8(key, base_flags, p + i0 * 1024, i0, (uint32_t(*)[8])cvs[i0]);
+    for (size_t i = i0; i < nleaves; i++) {
         size_t off = i * 1024, l = len - off < 1024 ? len - off : 1024;
         b3_leaf(key, base_flags, p + off, l, i, nleaves == 1, cvs[i]);
     }
@@ -336,7 +391,13 @@ static int64_t lz4_block(const uint8_t* src, size_t slen, uint8_t* dst, size_t d
         ml += 4;
         if (off == 0 || off > dpos - window_lo) return OZ_ERR_LZ4_BLOCK;
         if (ml > dcap - dpos) return OZ_ERR_SIZE_MISMATCH;
-        for (size_t i = 0; i < ml; i++) dst[dpos + i] = dst[dpos + i - off];
+        if (off >= ml) memcpy(dst + dpos, dst + dpos - off, ml); /* disjoint: plain copy */
+        else if (off >= 8) {                                      /* overlapping, period >= 8: 8-byte steps are exact */
+            size_t i = 0;
+            for (; i + 8 <= ml; i += 8) memcpy(dst + dpos + i, dst + dpos + i - off, 8);
+            for (; i < ml; i++) dst[dpos + i] = dst[dpos + i - off];
+        } else
+            for (size_t i = 0; i < ml; i++) dst[dpos + i] = dst[dpos + i - off]; /* byte-serial overlap semantics */
         dpos += ml;
     }
 }
