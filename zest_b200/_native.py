@@ -11,7 +11,7 @@ import subprocess
 import threading
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libzest_gpu.so")
+LIB_PATH = os.environ.get("ZEST_GPU_LIB") or os.path.join(_PKG, "libzest_gpu.so")  # override: developer A/B builds
 CSRC = os.path.join(_PKG, "csrc")
 
 ERR_NAMES = {
