@@ -279,6 +279,12 @@ def main():
     s1 = ctx.stats()
     clocks = sampler.stop() if rank == 0 else None
     e2e_val = all_bytes * K / t_e2e / 1e9
+    # what the link alone does: the same compressed bytes, pinned host -> device, nothing else (bounds e2e from above)
+    pin_t = torch.from_numpy(comp_host[:cpos])
+    for _ in range(2):
+        d_comp[:cpos].copy_(pin_t, non_blocking=True)
+    t_link = timed(lambda: d_comp[:cpos].copy_(pin_t, non_blocking=True), 5) / 5
+    link_gbps = cpos / t_link / 1e9
 
     # ---- per-kernel timing for the roofline (rank 0's numbers; same inputs, each stage alone)
     off = np.array([d.dst_off for d in descs], np.uint64)
@@ -333,7 +339,13 @@ def main():
     compressions = sum(oz.blake3_compressions(int(n)) for n in lens)
     int_ops = compressions * INT_OPS_PER_COMPRESSION
     sm_mhz = (clocks or {}).get("sm_mhz") or float(peaks.get("sm_max_mhz", 1965.0))
-    alu_peak_tops = 148 * 64 * sm_mhz * 1e6 / 1e12  # 16 lanes/clk/SMSP on the integer ALU pipe (B300_MICROARCH.md), at the observed clock
+    # integer-pipe calibration (zg_dev_int_pipe_peak): measured thread-op rates of the ALU pipe (LOP3/SHF/IADD3), the
+    # FMA pipe (IMAD) and both together.  The hash kernel issues, per 64-byte compression, 448 ALU-pipe and 336
+    # FMA-pipe instructions per thread (adds as IMAD), so its floor is max(448/alu, 336/fma, 784/both) per compression.
+    sink = torch.zeros(4, dtype=torch.uint8, device=dev)
+    g_alu, g_fma, g_both = C.c_double(), C.c_double(), C.c_double()
+    check(L.zg_dev_int_pipe_peak(sink.data_ptr(), C.byref(g_alu), C.byref(g_fma), C.byref(g_both), sp))
+    t_floor = compressions * max(448 / (g_alu.value * 1e9), 336 / (g_fma.value * 1e9), 784 / (g_both.value * 1e9))
     roofline = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 2), "peak": hbm_peak, "unit": "GB/s",
                 "frac": round(achieved / hbm_peak, 4), "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(alg[dom]), "avg_launch_ms": round(stages[dom] * 1e3, 4),
@@ -341,9 +353,14 @@ def main():
                                "uncompressed_GBps": round(total / t / 1e9, 2)} for s, t in stages.items()},
                 "blake3_alu": {"compressions": int(compressions), "int_ops": int(int_ops),
                                "achieved_Tops": round(int_ops / stages["blake3_hash"] / 1e12, 3),
-                               "peak_Tops": round(alu_peak_tops, 3), "frac": round(int_ops / stages["blake3_hash"] / 1e12 / alu_peak_tops, 4),
-                               "peak_source": f"148 SMs x 64 int lanes/clk x {sm_mhz:.0f} MHz observed (the ALU pipe alone; the kernel "
-                                              "issues its adds as IMAD on the FMA pipe, so frac can exceed 1)"}}
+                               "measured_pipe_peaks_Tops": {"alu": round(g_alu.value / 1e3, 2), "fma_imad": round(g_fma.value / 1e3, 2),
+                                                            "both": round(g_both.value / 1e3, 2)},
+                               "frac_of_alu_pipe": round(int_ops / stages["blake3_hash"] / 1e9 / g_alu.value, 4),
+                               "frac_of_issue_floor": round(t_floor / stages["blake3_hash"], 4),
+                               "note": "int_ops = 792 per compression (SURVEY.md 8d); the kernel issues 448 ALU-pipe + 336 "
+                                       "FMA-pipe (IMAD adds) thread-instructions per compression; issue floor = "
+                                       "max(448/alu, 336/fma, 784/both) from the measured pipe rates",
+                               "sm_mhz": sm_mhz}}
     cpu = None
     if not args.no_cpu:
         v, best, reps = cpu_arm(blobs, expected, total, cores)
@@ -358,7 +375,9 @@ def main():
         "e2e": {"value": round(e2e_val, 3), "unit": "GB/s", "ms_per_step": round(t_e2e / K * 1e3, 3),
                 "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) // K),
                 "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) // K),
-                "h2d_GBps": round((s1["h2d_bytes"] - s0["h2d_bytes"]) / t_e2e / 1e9, 2)},
+                "h2d_GBps": round((s1["h2d_bytes"] - s0["h2d_bytes"]) / t_e2e / 1e9, 2),
+                "h2d_link_GBps": round(link_gbps, 2),
+                "link_bound_GBps_uncompressed": round(link_gbps * total / comp_bytes, 2)},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
     }
     print(json.dumps(out), file=out_stream, flush=True)

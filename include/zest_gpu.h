@@ -201,6 +201,13 @@ ZG_API size_t zg_dev_cdc_scratch_bytes(uint64_t len);
 ZG_API int zg_dev_cdc(zg_ctx* ctx, const uint8_t* d_data, uint64_t len, uint64_t* d_ends, uint64_t cap, uint64_t* d_n_out,
                void* d_scratch, size_t scratch_bytes, void* stream);
 
+/* ---- measurement aid -------------------------------------------------------------------------------------------- */
+/* Measured peak of the SM's integer pipes in Gop/s (thread-level 32-bit operations): the ALU pipe (LOP3 / SHF / IADD3),
+ * the FMA pipe (IMAD) and both together.  bench.py reports the BLAKE3 kernel against these (SURVEY.md 8d asks for a
+ * calibrated integer roofline).  d_sink: any 4 writable device bytes.  Synchronises on `stream`.  No counterpart in
+ * zest. */
+ZG_API int zg_dev_int_pipe_peak(void* d_sink, double* alu_gops, double* fma_gops, double* both_gops, void* stream);
+
 /* ---- statistics -------------------------------------------------------------------------------------------- */
 typedef struct zg_stats {
     uint64_t calls, kernels_launched, h2d_bytes, d2h_bytes, bytes_decoded, chunks_hashed;

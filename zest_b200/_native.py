@@ -26,7 +26,7 @@ SYMBOLS = [
     "zg_hash_chunks", "zg_merkle_root", "zg_cdc", "zg_cdc_hash", "zg_dev_hash_scratch_bytes", "zg_dev_hash_chunks",
     "zg_dev_decode_scratch_bytes", "zg_dev_decode_chunks", "zg_dev_merkle_scratch_bytes", "zg_dev_merkle",
     "zg_dev_verify_scratch_bytes", "zg_dev_verify_xorbs", "zg_dev_cdc_scratch_bytes", "zg_dev_cdc", "zg_get_stats",
-    "zg_chunk_order", "zg_dev_hash_chunks_static", "zg_xorb_footer_bytes", "zg_xorb_footer",
+    "zg_chunk_order", "zg_dev_hash_chunks_static", "zg_xorb_footer_bytes", "zg_xorb_footer", "zg_dev_int_pipe_peak",
 ]
 
 
@@ -107,6 +107,7 @@ def lib() -> C.CDLL:
         L.zg_xorb_footer_bytes.argtypes = [sz]
         L.zg_xorb_footer_bytes.restype = sz
         L.zg_xorb_footer.argtypes = [vp, vp, vp, vp, sz, vp, sz, C.POINTER(sz)]
+        L.zg_dev_int_pipe_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), vp]
         L.zg_chunk_order.argtypes = [vp, sz]
         L.zg_chunk_order.restype = None
         _lib = L
