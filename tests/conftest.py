@@ -74,3 +74,76 @@ def footer_chunk_hashes(raw: bytes):
     p += 32 * n + 8 + 4 + 4 * n
     unc = np.array(struct.unpack("<%dI" % n, foot[p:p + 4 * n]), np.uint64)
     return hashes, unc, foot[8:40]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Hand-rolled LZ4 streams: sequences liblz4 / lz4_flex would never emit but the format allows (multi-byte length
+# extensions, matches longer than 64 KiB, offsets of 1 and 65535, empty literal runs, many tiny sequences).
+# ---------------------------------------------------------------------------------------------------------------
+def craft_lz4_block(rng, target_len: int, style: str):
+    """-> (block bytes, decoded bytes).  A valid LZ4 block of exactly target_len decoded bytes."""
+    out = bytearray()
+    blk = bytearray()
+
+    def emit(lit: bytes, mlen: int, off: int, last: bool):
+        tok_l = min(len(lit), 15)
+        tok_m = 0 if last else min(mlen - 4, 15)
+        blk.append((tok_l << 4) | tok_m)
+        if tok_l == 15:
+            r = len(lit) - 15
+            while r >= 255:
+                blk.append(255); r -= 255
+            blk.append(r)
+        blk.extend(lit)
+        out.extend(lit)
+        if last:
+            return
+        blk.extend(int(off).to_bytes(2, "little"))
+        if tok_m == 15:
+            r = mlen - 4 - 15
+            while r >= 255:
+                blk.append(255); r -= 255
+            blk.append(r)
+        for _ in range(mlen):
+            out.append(out[-off])
+
+    while True:
+        remaining = target_len - len(out)
+        if style == "tiny":
+            lit_n = int(rng.integers(0, 4))
+            mlen = int(rng.integers(4, 9))
+        elif style == "long":
+            lit_n = int(rng.choice([0, 1, 15, 16, 17, 270, 271, 600, 70000]))
+            mlen = int(rng.choice([4, 18, 19, 20, 21, 274, 275, 70000, 140000]))
+        else:
+            lit_n = int(rng.integers(0, 40))
+            mlen = int(rng.integers(4, 60))
+        if lit_n + mlen + 5 >= remaining or len(out) + lit_n == 0:
+            if remaining > 0 and len(out) + remaining > 0:
+                emit(bytes(rng.integers(0, 256, remaining, dtype=np.uint8)), 0, 0, True)
+            else:
+                emit(b"", 0, 0, True)
+            break
+        lit = bytes(rng.integers(0, 256, lit_n, dtype=np.uint8))
+        avail = len(out) + lit_n
+        if avail == 0:
+            continue
+        choice = int(rng.integers(0, 5))
+        off = [1, 2, min(avail, 65535), int(rng.integers(1, min(avail, 65535) + 1)), min(avail, 3)][choice]
+        emit(lit, mlen, off, False)
+    return bytes(blk), bytes(out)
+
+
+def frame_single_block(block: bytes, ulen: int) -> bytes:
+    """LZ4 frame around one compressed block, the way xet-core frames chunks."""
+    from oracle.xet_oracle import lib
+    import ctypes as C
+    bd = 0x70  # 4 MiB blocks: crafted blocks may be large
+    desc = bytes([0x60, bd])
+    hdr = np.frombuffer(desc, np.uint8).copy()
+    hc = (lib().oz_xxh32(hdr.ctypes.data, 2, 0) >> 8) & 0xFF
+    return b"\x04\x22\x4d\x18" + desc + bytes([hc]) + len(block).to_bytes(4, "little") + block + b"\x00\x00\x00\x00"
+
+
+def chunk_record(payload: bytes, scheme: int, ulen: int) -> bytes:
+    return bytes([0]) + len(payload).to_bytes(3, "little") + bytes([scheme]) + ulen.to_bytes(3, "little") + payload

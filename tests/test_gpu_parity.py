@@ -157,6 +157,48 @@ def test_frame_variants(ctx, oracle, fflags, block_max):
             assert got.verdict[0] == want[0] and want[0] < 0
 
 
+def test_crafted_streams(ctx, oracle):
+    """Hand-rolled LZ4 blocks that no real compressor emits but the format allows: multi-byte length extensions,
+    matches beyond 64 KiB (the record splitter), offsets of 1, 2, 3 and 65535, empty literal runs, thousands of tiny
+    sequences -- as scheme 1 and (through the byte-grouping inverse) scheme 2; then random corruptions of them must
+    get the oracle's verdict."""
+    from conftest import chunk_record, craft_lz4_block, frame_single_block
+    rng = np.random.default_rng(78)
+    records, wants = [], []
+    for style, n in [("tiny", 5000), ("mixed", 60000), ("long", 900000), ("long", 300001), ("tiny", 9), ("mixed", 1),
+                     ("mixed", 131072), ("tiny", 70003), ("long", 2_000_000)]:
+        blk, want = craft_lz4_block(rng, n, style)
+        frame = frame_single_block(blk, len(want))
+        records.append(chunk_record(frame, 1, len(want))); wants.append(want)
+        # scheme 2: the decoded block is the grouped form of some data; regroup it to get the expected bytes
+        g = np.frombuffer(want, np.uint8)
+        q, r = divmod(g.size, 4)
+        sizes = [q + (k < r) for k in range(4)]
+        planes = np.split(g, np.cumsum(sizes)[:-1])
+        inter = np.empty(g.size, np.uint8)
+        for k in range(4):
+            inter[k::4] = planes[k]
+        records.append(chunk_record(frame, 2, len(want))); wants.append(inter.tobytes())
+    stream = b"".join(records)
+    n = len(records)
+    assert oracle.extract_chunk_range(stream, 0, n) == b"".join(wants)
+    assert z.XorbReader(stream, ctx).extract_chunk_range(0, n) == b"".join(wants)
+    for i in (0, 3, 4, 9, n - 1):
+        assert z.XorbReader(stream, ctx).extract_chunk_range(i, i + 1) == wants[i]
+    # corruptions: same verdicts as the oracle, xorb by xorb
+    blobs = []
+    for _ in range(60):
+        b = bytearray(records[int(rng.integers(0, n))])
+        for _ in range(int(rng.integers(1, 4))):
+            b[int(rng.integers(8, len(b)))] ^= 1 << int(rng.integers(0, 8))
+        blobs.append(bytes(b))
+    got = z.verify_xorbs(blobs, ctx=ctx)
+    want_v, want_roots, _ = oracle.verify_xorbs(blobs, threads=8)
+    assert list(got.verdict) == list(want_v)
+    ok = want_v >= 0
+    assert (got.roots[ok] == want_roots[ok]).all()
+
+
 def test_special_streams(ctx, oracle):
     """Long matches (zeros, period-3, period-40), a one-byte file, an empty xorb list, an empty blob."""
     cases = [np.zeros(300_000, np.uint8), np.tile(np.frombuffer(b"abc", np.uint8), 100_000),

@@ -141,3 +141,13 @@ def test_corruption_detected(oracle, vectors):
     assert oracle.verify_xorbs([stream[:-5]], expected=[xorb_hash])[0][0] == -3
     bad = bytearray(stream); bad[8] ^= 1             # LZ4 frame magic
     assert oracle.verify_xorbs([bytes(bad)], expected=[xorb_hash])[0][0] == -6
+
+
+def test_crafted_streams(oracle):
+    """Hand-rolled LZ4 blocks (length extensions, > 64 KiB matches, offsets 1 / 65535) decode exactly."""
+    from conftest import chunk_record, craft_lz4_block, frame_single_block
+    rng = np.random.default_rng(77)
+    for style, n in [("tiny", 5000), ("mixed", 60000), ("long", 900000), ("long", 300000), ("tiny", 9), ("mixed", 1)]:
+        blk, want = craft_lz4_block(rng, n, style)
+        stream = chunk_record(frame_single_block(blk, len(want)), 1, len(want))
+        assert oracle.extract_chunk_range(stream, 0, 1) == want
