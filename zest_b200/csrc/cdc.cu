@@ -113,9 +113,10 @@ __global__ void __launch_bounds__(kThreads) cdc_scan_kernel(const uint8_t* __res
 // Pass 2: the min/max rule over the sparse candidate stream.  The rule is a chain (each cut depends on the previous
 // one), but the chain forgets quickly: a walker started at an arbitrary position agrees with the true one as soon as
 // both cut at the same candidate, usually within one or two chunks.  So the tile list is split into segments; every
-// segment is walked speculatively (as if a cut fell exactly on its first byte) by its own thread, and a single thread
-// then stitches: it carries the true state into each segment, walks until one of its cuts equals one of the
-// segment's speculative cuts, and adopts the rest of that list.  A last kernel gathers the pieces in order.
+// segment is walked speculatively (as if a cut fell exactly on its first byte) by its own thread; a second parallel
+// pass walks every segment from the state its predecessor's speculation ends in until one of its cuts equals one
+// of the segment's own speculative cuts, and adopts the rest of that list; one warp checks that every predecessor did
+// join (else it repairs serially from there) and a last kernel gathers the pieces in order.
 // ---------------------------------------------------------------------------------------------------------------
 
 struct SegInfo {       // 32 bytes per segment
@@ -225,53 +226,120 @@ __device__ bool walk_tiles(const uint8_t* __restrict__ data, uint64_t len, const
     return stop;
 }
 
-__global__ void __launch_bounds__(32) cdc_stitch_kernel(const uint8_t* __restrict__ data, uint64_t len,
+// The true walk of segment k from entry state s: cuts that differ from the segment's speculation go to its private
+// list until one coincides with a speculative cut (the join); from there the speculation is adopted.  Fills
+// g.join / g.priv_n / g.pad (1 = joined) and returns the state after the segment.
+__device__ uint64_t stitch_segment(const uint8_t* __restrict__ data, uint64_t len, const TileRec* __restrict__ tiles,
+                                   uint64_t n_tiles, uint32_t seg_tiles, uint32_t cap, uint32_t k, uint64_t s, SegInfo& g,
+                                   const uint64_t* __restrict__ spec, uint64_t* __restrict__ priv, bool& overflow) {
+    const uint64_t t0 = (uint64_t)k * seg_tiles, t1 = t0 + seg_tiles < n_tiles ? t0 + seg_tiles : n_tiles;
+    const uint64_t seg_end = t1 * (uint64_t)kTileBytes < len ? t1 * (uint64_t)kTileBytes : len;
+    const uint64_t* sp = spec + (size_t)k * cap;
+    CutSink pv{priv + (size_t)k * cap, 0, cap, false};
+    uint32_t j = 0;
+    bool joined = false;
+    auto put = [&](uint64_t e) -> bool {
+        if (!g.dense) {
+            while (j < g.spec_n && sp[j] < e) j++;
+            if (j < g.spec_n && sp[j] == e) { joined = true; return true; }
+        }
+        pv.put(e);
+        return false;
+    };
+    if (s == t0 * (uint64_t)kTileBytes && !g.dense) {
+        joined = true;  // the speculation started from the true state (always so for segment 0)
+        j = 0;
+    } else {
+        if (g.cand_n != 0 || g.dense) walk_tiles(data, len, tiles, t0, t1, s, put);
+        if (!joined) while (seg_end - s >= kMax && seg_end > s && !joined) { s += kMax; if (put(s)) break; }
+    }
+    g.priv_n = pv.n;
+    g.join = joined ? j : g.spec_n;
+    g.pad = joined ? 1u : 0u;
+    if (pv.overflow) overflow = true;
+    if (joined && g.spec_n > g.join) s = sp[g.spec_n - 1];
+    return s;
+}
+
+// Every segment's true walk at once, each entered with the state its predecessor's speculation ends in.  That guess is
+// right whenever the predecessor's own true walk joins its speculation -- which is the normal case -- and then the
+// exit state of a segment does not depend on how it was entered.
+__global__ void __launch_bounds__(128) cdc_join_kernel(const uint8_t* __restrict__ data, uint64_t len,
+                                                       const TileRec* __restrict__ tiles, uint64_t n_tiles,
+                                                       uint32_t seg_tiles, uint32_t n_segs, uint32_t cap,
+                                                       SegInfo* __restrict__ segs, const uint64_t* __restrict__ spec,
+                                                       uint64_t* __restrict__ priv) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_segs) return;
+    SegInfo g = segs[k];
+    uint64_t s = 0;
+    if (k > 0) {
+        const SegInfo p = segs[k - 1];  // only spec_n / dense are read, which cdc_spec_kernel wrote
+        s = (p.dense || p.spec_n == 0) ? (uint64_t)(k - 1) * seg_tiles * (uint64_t)kTileBytes
+                                       : spec[(size_t)(k - 1) * cap + p.spec_n - 1];
+    }
+    bool overflow = false;
+    const uint64_t exit_s = stitch_segment(data, len, tiles, n_tiles, seg_tiles, cap, k, s, g, spec, priv, overflow);
+    g.base = exit_s;  // carried to the finishing kernel, which turns it into the output position
+    if (overflow) g.pad |= 2u;
+    // join / priv_n / pad / base only: spec_n, cand_n and dense are read by the neighbour's thread
+    segs[k].join = g.join; segs[k].priv_n = g.priv_n; segs[k].pad = g.pad; segs[k].base = g.base;
+}
+
+// One warp: validate the chain of guesses (segment k's guess holds iff segment k-1 joined), repair serially from
+// the first segment that did not join (pathological inputs only), and turn counts into output positions.
+__global__ void __launch_bounds__(32) cdc_finish_kernel(const uint8_t* __restrict__ data, uint64_t len,
                                                         const TileRec* __restrict__ tiles, uint64_t n_tiles,
                                                         uint32_t seg_tiles, uint32_t n_segs, uint32_t cap,
                                                         SegInfo* __restrict__ segs, const uint64_t* __restrict__ spec,
                                                         uint64_t* __restrict__ priv, uint64_t* __restrict__ n_out,
                                                         uint64_t out_cap) {
-    if (threadIdx.x != 0) return;
-    uint64_t s = 0, total = 0;
-    bool overflow = false;
-    for (uint32_t k = 0; k < n_segs; k++) {
-        const uint64_t t0 = (uint64_t)k * seg_tiles, t1 = t0 + seg_tiles < n_tiles ? t0 + seg_tiles : n_tiles;
-        const uint64_t seg_end = t1 * (uint64_t)kTileBytes < len ? t1 * (uint64_t)kTileBytes : len;
-        SegInfo g = segs[k];
-        const uint64_t* sp = spec + (size_t)k * cap;
-        CutSink pv{priv + (size_t)k * cap, 0, cap, false};
-        uint32_t j = 0;
-        bool joined = false;
-        auto put = [&](uint64_t e) -> bool {
-            if (!g.dense) {
-                while (j < g.spec_n && sp[j] < e) j++;
-                if (j < g.spec_n && sp[j] == e) { joined = true; return true; }
-            }
-            pv.put(e);
-            return false;
-        };
-        if (s == t0 * (uint64_t)kTileBytes && !g.dense) {
-            joined = true;  // the speculation started from the true state (always so for segment 0)
-            j = 0;
-        } else {
-            if (g.cand_n != 0 || g.dense) walk_tiles(data, len, tiles, t0, t1, s, put);
-            if (!joined) while (seg_end - s >= kMax && seg_end > s && !joined) { s += kMax; if (put(s)) break; }
-        }
-        g.base = total;
-        g.priv_n = pv.n;
-        g.join = joined ? j : g.spec_n;
-        if (pv.overflow) overflow = true;
-        total += pv.n + (g.spec_n - g.join);
-        if (joined && g.spec_n > g.join) s = sp[g.spec_n - 1];
-        segs[k] = g;
+    const uint32_t lane = threadIdx.x;
+    // first segment whose walk did not join (its successor's guess is then wrong)
+    uint32_t first_bad = n_segs;
+    for (uint32_t k0 = 0; k0 < n_segs && first_bad == n_segs; k0 += 32) {
+        const uint32_t k = k0 + lane;
+        const bool bad = k < n_segs && (segs[k].pad & 1u) == 0;
+        const uint32_t m = __ballot_sync(0xffffffffu, bad);
+        if (m) first_bad = k0 + (uint32_t)__ffs(m) - 1;
     }
-    // whatever is left after the last cut is the final (possibly short) chunk
-    uint64_t extra = 0;
-    uint64_t* tail = priv + (size_t)n_segs * cap;  // room for one more entry
-    if (len > s) { tail[0] = len; extra = 1; }
-    n_out[0] = total + extra;
-    n_out[1] = (overflow || total + extra > out_cap) ? 1 : 0;
-    n_out[2] = total;  // where the tail entry goes
+    bool overflow = false;
+    uint64_t s = 0;
+    const uint32_t n_ok = first_bad < n_segs ? first_bad + 1 : n_segs;  // segments [0, n_ok) were entered correctly
+    if (lane == 0) {
+        if (n_ok > 0) s = segs[n_ok - 1].base;  // exit state of the last correctly entered segment
+        for (uint32_t k = n_ok; k < n_segs; k++) {  // serial repair
+            SegInfo g = segs[k];
+            s = stitch_segment(data, len, tiles, n_tiles, seg_tiles, cap, k, s, g, spec, priv, overflow);
+            segs[k] = g;
+        }
+    }
+    __syncwarp();
+    // output positions: exclusive prefix sum of per-segment counts (32 segments per pass)
+    uint64_t total = 0;
+    for (uint32_t k0 = 0; k0 < n_segs; k0 += 32) {
+        const uint32_t k = k0 + lane;
+        uint64_t c = 0;
+        if (k < n_segs) { c = (uint64_t)segs[k].priv_n + (segs[k].spec_n - segs[k].join); if (segs[k].pad & 2u) overflow = true; }
+        uint64_t x = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint64_t y = __shfl_up_sync(0xffffffffu, x, d);
+            if (lane >= (uint32_t)d) x += y;
+        }
+        if (k < n_segs) segs[k].base = total + x - c;
+        total += __shfl_sync(0xffffffffu, x, 31);
+    }
+    const uint32_t any_over = __ballot_sync(0xffffffffu, overflow);
+    if (lane == 0) {
+        // whatever is left after the last cut is the final (possibly short) chunk
+        uint64_t extra = 0;
+        uint64_t* tail = priv + (size_t)n_segs * cap;  // room for one more entry
+        if (len > s) { tail[0] = len; extra = 1; }
+        n_out[0] = total + extra;
+        n_out[1] = (any_over || total + extra > out_cap) ? 1 : 0;
+        n_out[2] = total;  // where the tail entry goes
+    }
 }
 
 __global__ void __launch_bounds__(128) cdc_gather_kernel(const SegInfo* __restrict__ segs, uint32_t n_segs, uint32_t cap,
@@ -329,7 +397,8 @@ cudaError_t launch_cdc(const uint8_t* data, uint64_t len, uint64_t* ends, uint64
         cdc_scan_kernel<<<(unsigned)L.n_tiles, kThreads, 0, st>>>(data, len, tiles);
         cdc_spec_kernel<<<(L.n_segs + 127) / 128, 128, 0, st>>>(tiles, L.n_tiles, len, L.seg_tiles, L.n_segs, L.cap, segs, spec);
     }
-    cdc_stitch_kernel<<<1, 32, 0, st>>>(data, len, tiles, L.n_tiles, L.seg_tiles, L.n_segs, L.cap, segs, spec, priv, n_out, cap);
+    if (L.n_segs) cdc_join_kernel<<<(L.n_segs + 127) / 128, 128, 0, st>>>(data, len, tiles, L.n_tiles, L.seg_tiles, L.n_segs, L.cap, segs, spec, priv);
+    cdc_finish_kernel<<<1, 32, 0, st>>>(data, len, tiles, L.n_tiles, L.seg_tiles, L.n_segs, L.cap, segs, spec, priv, n_out, cap);
     cdc_gather_kernel<<<L.n_segs + 1, 128, 0, st>>>(segs, L.n_segs, L.cap, spec, priv, n_out, ends, cap);
     return cudaGetLastError();
 }
