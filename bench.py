@@ -154,7 +154,9 @@ def main():
     host_threads = max(1, cores // max(world, 1)) if args.impl == "ours" else cores
     config = {"workload": wl["desc"], "name": args.workload, "uncompressed_bytes_per_rank": nbytes,
               "l2_policy": "inputs larger than L2 (compressed + decoded working set >> 126 MB), no flush needed",
-              "parallelism": f"xorb-sharded x{world}, no collective"}
+              "parallelism": f"xorb-sharded x{world}, no collective",
+              "chunk_index": "host walk of the 8-byte chunk headers (zg_xorb_index): inside the timed region of e2e; "
+                             "value starts from blobs + 32-byte chunk descriptors in HBM"}
 
     # ------------------------------------------------------------------ reference arm: CPU only, rank 0 only
     if args.impl == "reference":

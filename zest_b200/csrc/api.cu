@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -411,16 +412,18 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
     if (bytes_verified) *bytes_verified = 0;
     if (n == 0) return ZG_OK;
     ctx->calls++;
-    // Up to four lanes: the copies of one sub-batch overlap the kernels of the others and the host walk of the next.
+    // Up to four lanes (ZEST_VERIFY_LANES): the copies of one sub-batch overlap the kernels of the others and the host walk of the next.
     // Several sub-batches in flight also matter for the decoder itself: one LZ4 chunk is a serial chain of a few
     // milliseconds, so a single ~128 MB sub-batch cannot fill the GPU; three or four of them on separate streams do.
     constexpr int kMaxSlots = 8;
-    LaneGuard g0(ctx), g1(ctx, false), g2(ctx, false), g3(ctx, false), g4(ctx, false), g5(ctx, false), g6(ctx, false), g7(ctx, false);
+    std::unique_ptr<LaneGuard> guards[kMaxSlots];
     VerifySlot slots[kMaxSlots];
-    Lane* got[kMaxSlots] = {g0.l, g1.l, g2.l, g3.l, g4.l, g5.l, g6.l, g7.l};
     int n_slots = 0;
-    for (int i = 0; i < kMaxSlots && n_slots < max_verify_lanes(); i++)
-        if (got[i]) slots[n_slots++].L = got[i];
+    for (int i = 0; i < kMaxSlots && i < max_verify_lanes(); i++) {
+        guards[i].reset(new LaneGuard(ctx, /*wait=*/i == 0));  // the first lane is waited for, the others only if free
+        if (!guards[i]->l) { guards[i].reset(); break; }
+        slots[n_slots++].L = guards[i]->l;
+    }
     size_t hashes_written = 0;
     uint64_t verified = 0;
 
