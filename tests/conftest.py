@@ -14,6 +14,12 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # the product library is built in-tree by __graft_entry__.build(); build it here if a fresh checkout has none
+    # (nvcc cross-compiles without a GPU).  The tests never fall back to anything else.
+    lib = os.path.join(ROOT, "zest_b200", "libzest_gpu.so")
+    if not os.path.exists(lib):
+        import subprocess
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "zest_b200", "csrc"), "-j8"], stdout=subprocess.DEVNULL)
 
 
 @pytest.fixture(scope="session")
