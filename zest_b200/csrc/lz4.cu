@@ -6,23 +6,36 @@
 // lz4_block, oz_decode_chunk), whose checks are mirrored one for one and in the same order so that a malformed
 // chunk gets the same error code on both sides.
 //
-// Mapping.  LZ4 token parsing is serial inside a chunk, and on real Xet data the sequences are tiny (bf16
-// byte-grouped: ~4,100 sequences per 64 KiB chunk, ~8 output bytes each outside the two incompressible planes),
-// so the per-sequence instruction count decides throughput.  A warp therefore works on up to 32 chunks at once:
-//   parse   : LANE c walks the token stream of chunk slot c on its own (no warp-wide work per token) and appends
-//             validated (literal source, destination, literal length, match length, offset) records to a
-//             shared-memory list -- all format and bounds checks happen here, on positions only;
-//   execute : for each slot, LANE s performs sequence s of the list: short literal runs and short matches are
-//             copied by their own lane, long ones (the 16-40 KB incompressible planes, zero runs) by the whole
-//             warp with word-wide, funnel-shifted copies; matches wait on earlier matches of the same batch only
-//             when their source overlaps them (frontier test), so most batches finish in one or two rounds.
-// Chunks are handed out through a global ticket counter, so slots refill as soon as a chunk ends.  Output goes to
-// global memory (a 64 MiB xorb stays resident in the 126 MB L2); byte-group regrouping is done by the warp when a
-// scheme-2 chunk completes, reading the planes back from L2.
+// Mapping.  One warp decodes one chunk at a time (chunks are handed out longest-first through a ticket counter).
+// LZ4's token stream is serial, and on real Xet data the sequences are tiny (text: ~5,900 per 64 KiB chunk, ~11
+// output bytes each), so a lane-serial walk leaves 31 lanes idle and costs ~100 warp instructions per sequence.
+// The walk is therefore SPECULATIVE and warp-wide:
+//   parse   : the next 32 x 68 stream bytes of the block are staged in shared memory and cut into 32 segments;
+//             lane k walks tokens from the first byte of segment k as if a sequence started there.  Lane 0 starts
+//             at the true position.  A chain that starts on a wrong byte falls onto true sequence boundaries
+//             after a few hops (every hop lands on a boundary with probability ~1/sequence length, and once on
+//             one it stays on them), so each lane also walks a few hops into its neighbour's segment until it
+//             reaches a position its neighbour visited -- the JOIN.  Positions visited are kept in a byte map.
+//   resolve : lane 0 is true; a lane is true from its join index on iff the chain before it is true and joined
+//             it (pointer doubling over the join links, 5 shuffle rounds).  True records are numbered in stream
+//             order by a warp scan.  A chain that meets anything unusual (block end near, oversized length, zero
+//             offset) simply stops; if it was the true chain, the serial walker takes over from that byte.
+//   execute : 32 consecutive true sequences per step, one per lane: output positions by a warp scan of the lengths,
+//             the offset/size checks of the oracle on those positions, then literals and matches whose source
+//             precedes the step in one pass, and the few matches that read the step's own output in frontier
+//             rounds.  Long runs (incompressible planes, zero runs) are copied by the whole warp.
+//   serial  : frame and block headers, the last bytes of a block, stored blocks, oversized pieces and every error
+//             go through a plain one-sequence-at-a-time walker that mirrors the oracle check for check; it runs
+//             uniformly on all lanes (same instructions, no broadcasts) and feeds the same execute step.
+// Output goes to global memory (a 64 MiB xorb stays resident in the 126 MB L2); byte-group regrouping is done by
+// the warp when a scheme-2 chunk completes, reading the planes back from L2.
 //
 // Roofline: HBM-bound in principle (compressed bytes in + decoded bytes out); in practice bounded by issue slots
-// and L1 wavefronts per sequence.  bench.py reports achieved GB/s over those algorithmic bytes.
+// and dependent-instruction latency per sequence.  bench.py reports achieved GB/s over those algorithmic bytes.
+#include <cuda_runtime.h>
+
 #include <algorithm>
+#include <cstdint>
 #include <cstdlib>
 #include <vector>
 
@@ -32,29 +45,31 @@ namespace zg {
 
 namespace {
 
-constexpr int kWarps = 1;          // warps per CTA (no block-level cooperation; small CTAs spread over all SMs)
-constexpr int kSeqCap = 16;        // records parsed per slot per round (two slots share one 32-lane execute step)
-constexpr uint32_t kShort = 16;    // literal runs / matches up to this length are copied by their own lane
+constexpr uint32_t kFull = 0xffffffffu;
+constexpr uint32_t kShort = 16;       // literal runs / matches up to this length are copied by their own lane
 constexpr uint32_t kMaxPiece = 65535;
+constexpr uint32_t kSerialCap = 16;   // sequences per round of the serial walker
+constexpr uint32_t kSeg = 68;         // speculative segment, stream bytes: 17 words, so 32 lanes start in 32 banks
+constexpr uint32_t kCap = 24;         // a 68-byte segment holds at most 23 sequences
+constexpr uint32_t kJoinHops = 64;    // sequences a chain may walk beyond its segment looking for its join
+constexpr uint32_t kPool = 704;       // records per round, all lanes together (slots are handed out per iteration)
+constexpr uint32_t kSpanMax = 32 * kSeg;
+constexpr uint32_t kWinBytes = 2304;  // staged stream bytes: alignment slack + span + >= 100 bytes beyond it
+constexpr int32_t kNotTrue = INT32_MIN;
+constexpr uint32_t kSpecMin = 32;     // blocks (or block remainders) shorter than this go to the serial walker
 
 enum : int { ST_IDLE = 0, ST_START, ST_BLOCK_HDR, ST_IN_BLOCK, ST_AFTER_BLOCK, ST_FINISH, ST_EXHAUSTED };
 
-struct Seq {           // 16 bytes
-    uint32_t lit_src;  // literal source, relative to the chunk payload
-    uint32_t dst;      // destination of the literals, relative to the chunk's LZ4 output
-    uint32_t lens;     // literal length | match length << 16
-    uint32_t off;      // match offset (1..65535)
-};
-
 struct WarpShared {
-    Seq rec[kSeqCap * 32];         // record s of slot c lives at [s * 32 + (c ^ s)] (conflict-free both ways)
-    unsigned long long src[32];    // per slot: payload base
-    unsigned long long lz[32];     // per slot: LZ4 output base
-    uint32_t pend[32];             // per slot: records whose match is still to be copied (bit s)
-    uint32_t frontier[32];         // per slot: output offset below which everything is final this round
-    uint32_t w0[32];               // per slot: output offset where this round's records start
-    uint8_t first[32];             // per slot: index of the first pending match
-    uint8_t cnt[32];               // per slot: records parsed this round
+    uint4 win[kWinBytes / 16];       // staged stream window
+    uint4 idx[kSpanMax / 16];        // byte map over the span: 1 + record index of the home chain at that byte, else 0
+    uint2 pool[kPool];               // records of the round: {pos - ip | lit << 16, ml | off << 16}
+    uint16_t meta[kPool];            // per record: lane << 8 | number of the record within its lane's chain
+    uint16_t ref[kPool];             // true records in stream order: pool slot
+    uint32_t sj[32];                 // per lane: number of its first true record, posted by the chain that joins it
+    uint32_t first[32];              // per lane: the same, for everyone to read
+    int32_t base[32];                // per lane: stream-order index of its record number 0 (kNotTrue: lane not true)
+    uint32_t srec[kSerialCap * 3];   // serial walker records: literal source, lit | ml << 16, offset
 };
 
 __device__ __forceinline__ uint32_t rd8(const uint8_t* p) { return __ldg(p); }
@@ -192,107 +207,186 @@ __device__ __forceinline__ void warp_regroup(uint8_t* out, const uint8_t* tmp, u
     }
 }
 
-// ---- execute steps.  A 32-lane step covers two slots x 16 records (slot = base + lane / 16, record = lane % 16); NP = 2
-// issues two such steps back to back so the loads of four slots are in flight together, NP = 1 is used when the
-// second pair of slots is empty (small batches run with 1-2 slots per warp).
 
-// Pass 1: every literal run, and every match whose source lies wholly before this round's output.
-template <int NP>
-__device__ __forceinline__ void exec_pass1(WarpShared& ws, uint32_t it, uint32_t lane) {
-    const uint32_t half = lane >> 4, s = lane & 15;
-    Seq e[NP];
-    uint32_t lit[NP], ml[NP], n[NP], k[NP], c[NP], x[NP][4], y[NP][4];
-    const uint8_t* sp[NP];
-    uint8_t* dp[NP];
-    bool old[NP];
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const uint32_t sa = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// Stage kWinBytes of the stream starting at the 16-byte-aligned address A (clipped at the padded end of the
+// compressed buffer) and clear the position map.  Asynchronous: wait + __syncwarp before use.
+__device__ __forceinline__ void stage_window(WarpShared& ws, uintptr_t A, const uint8_t* comp_hi, uint32_t lane) {
+    const uint8_t* g = reinterpret_cast<const uint8_t*>(A);
 #pragma unroll
-    for (int q = 0; q < NP; q++) {
-        c[q] = 2 * it + half + 2 * q;
-        e[q] = Seq{0, 0, 0, 0};
-        if (s < ws.cnt[c[q]]) e[q] = ws.rec[s * 32 + (c[q] ^ s)];
-        lit[q] = e[q].lens & 0xffffu; ml[q] = e[q].lens >> 16;
-        sp[q] = reinterpret_cast<const uint8_t*>(ws.src[c[q]]) + e[q].lit_src;
-        dp[q] = reinterpret_cast<uint8_t*>(ws.lz[c[q]]) + e[q].dst;
-        n[q] = lit[q] <= kShort ? lit[q] : 0u;
-        // "old" match: short, and its source ends at or before the first byte this round produces for the slot
-        old[q] = ml[q] != 0 && ml[q] <= kShort && e[q].dst + lit[q] - e[q].off + ml[q] <= ws.w0[c[q]];
-        k[q] = old[q] ? ml[q] : 0u;
-    }
+    for (uint32_t i = lane; i < kWinBytes / 16; i += 32)
+        if (g + 16 * i + 16 <= comp_hi) cp_async16(&ws.win[i], g + 16 * i);
 #pragma unroll
-    for (int q = 0; q < NP; q++) load16<true>(sp[q], n[q], x[q]);
-#pragma unroll
-    for (int q = 0; q < NP; q++) load16<false>(dp[q] + lit[q] - e[q].off, k[q], y[q]);
-#pragma unroll
-    for (int q = 0; q < NP; q++) store16(dp[q], n[q], x[q]);
-#pragma unroll
-    for (int q = 0; q < NP; q++) store16(dp[q] + lit[q], k[q], y[q]);
-#pragma unroll
-    for (int q = 0; q < NP; q++) {
-        if (old[q]) atomicAnd(&ws.pend[c[q]], ~(1u << s));
-        uint32_t lm = __ballot_sync(0xffffffffu, lit[q] > kShort);  // long literal runs: whole-warp copies
-        while (lm) {
-            int l = __ffs(lm) - 1;
-            lm &= lm - 1;
-            uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dp[q]), l));
-            const uint8_t* g = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(sp[q]), l));
-            warp_copy<false>(d, g, __shfl_sync(0xffffffffu, lit[q], l), lane);
+    for (uint32_t i = lane; i < kSpanMax / 16; i += 32) ws.idx[i] = make_uint4(0, 0, 0, 0);
+}
+
+// One speculative hop: the sequence whose token sits at stream position pos (relative to the chunk payload).
+// Positional checks only; anything unusual makes the chain stop in front of this sequence (ok = false).
+// wofs = window offset of stream position 0 (may wrap), so position p sits at window byte p + wofs.
+struct Hop {
+    uint32_t lit, ml, off, nip;
+    bool ok;
+};
+__device__ __forceinline__ uint32_t stream_byte(const uint8_t* src, const uint8_t* win, uint32_t wofs, uint32_t p) {
+    const uint32_t r = p + wofs;
+    return r < kWinBytes ? (uint32_t)win[r] : rd8(src + p);
+}
+__device__ __noinline__ Hop spec_hop_general(const uint8_t* src, const uint8_t* win, uint32_t wofs, uint32_t pos, uint32_t bend);
+
+// The common case without a branch: at most one extension byte per length, everything inside the staged window.
+// Two dependent shared-memory reads: token + first literal-length byte, then offset + first match-length byte.
+__device__ __forceinline__ Hop spec_hop(const uint8_t* src, const uint8_t* win, uint32_t wofs, uint32_t pos, uint32_t bend) {
+    const uint32_t r = pos + wofs;
+    if (r <= kWinBytes - 8) {
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(win + (r & ~3u));
+        const uint32_t t = __funnelshift_r(w[0], w[1], (r & 3u) * 8);
+        const uint32_t tok = t & 0xffu, e1 = (t >> 8) & 0xffu;
+        const uint32_t lit4 = tok >> 4, ml4 = tok & 15u;
+        const bool lx = lit4 == 15u, mx = ml4 == 15u;
+        const uint32_t lit = lit4 + (lx ? e1 : 0u);
+        const uint32_t o = 1u + (lx ? 1u : 0u) + lit;  // the offset's distance from the token
+        const uint32_t r2 = r + o;
+        if (r2 <= kWinBytes - 8) {
+            const uint32_t* v = reinterpret_cast<const uint32_t*>(win + (r2 & ~3u));
+            const uint32_t u = __funnelshift_r(v[0], v[1], (r2 & 3u) * 8);
+            const uint32_t e2 = (u >> 16) & 0xffu;
+            if (!((lx && e1 == 255u) || (mx && e2 == 255u))) {
+                Hop h;
+                h.lit = lit; h.off = u & 0xffffu; h.ml = ml4 + 4u + (mx ? e2 : 0u);
+                h.nip = pos + o + 2u + (mx ? 1u : 0u);
+                h.ok = h.nip <= bend && h.off != 0;  // offset (and extension byte) inside the block
+                return h;
+            }
         }
+    }
+    return spec_hop_general(src, win, wofs, pos, bend);
+}
+
+__device__ __noinline__ Hop spec_hop_general(const uint8_t* src, const uint8_t* win, uint32_t wofs, uint32_t pos, uint32_t bend) {
+    Hop h;
+    h.ok = false; h.lit = h.ml = h.off = 0; h.nip = pos;
+    const uint32_t r = pos + wofs;
+    uint64_t w64;
+    if (r <= kWinBytes - 12) {
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(win + (r & ~3u));
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], sh = (r & 3u) * 8;
+        w64 = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
+    } else
+        w64 = load_window(src + pos);
+    const uint32_t tok = (uint32_t)w64 & 0xffu;
+    uint32_t lit = tok >> 4, ml = tok & 15u, q = pos + 1;
+    if (lit == 15u) {
+        uint32_t b;
+        do {
+            if (q >= bend) return h;
+            b = (q - pos < 8) ? (uint32_t)(w64 >> (8 * (q - pos))) & 0xffu : stream_byte(src, win, wofs, q);
+            q++;
+            lit += b;
+            if (lit > kMaxPiece) return h;
+        } while (b == 255u);
+    }
+    const uint32_t o = q + lit;  // position of the offset
+    if (o + 2 > bend) return h;  // includes the literals-only last sequence of a block
+    uint32_t off;
+    if (o - pos <= 6) off = (uint32_t)(w64 >> (8 * (o - pos))) & 0xffffu;
+    else off = stream_byte(src, win, wofs, o) | (stream_byte(src, win, wofs, o + 1) << 8);
+    q = o + 2;
+    if (ml == 15u) {
+        uint32_t b;
+        do {
+            if (q >= bend) return h;
+            b = (q - pos < 8) ? (uint32_t)(w64 >> (8 * (q - pos))) & 0xffu : stream_byte(src, win, wofs, q);
+            q++;
+            ml += b;
+            if (ml > kMaxPiece - 4) return h;
+        } while (b == 255u);
+    }
+    ml += 4;
+    if (off == 0) return h;
+    h.lit = lit; h.ml = ml; h.off = off; h.nip = q; h.ok = true;
+    return h;
+}
+
+// One execute step: up to 32 consecutive sequences of one chunk in stream order, one per lane (lanes without a
+// sequence pass lit = ml = 0).  dst is the sequence's output position, op0 the position of the step's first byte;
+// everything below op0 is final.  Pass 1 copies every literal run and every match whose source lies wholly below
+// op0 (most of them); the rest wait for the frontier -- the start of the lowest match still pending, below which
+// all bytes are final -- and usually go in one or two more rounds.
+__device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint32_t op0, uint32_t lit_src, uint32_t lit,
+                                           uint32_t ml, uint32_t off, uint32_t dst, uint32_t lane) {
+    __syncwarp();
+    const uint8_t* sp = src + lit_src;
+    uint8_t* dp = lz + dst;
+    const uint32_t md = dst + lit;  // where the match goes
+    uint8_t* mp = lz + md;
+    {
+        uint32_t x[4], y[4];
+        const uint32_t n = lit <= kShort ? lit : 0u;
+        const bool old = ml != 0 && ml <= kShort && md - off + ml <= op0;
+        const uint32_t k = old ? ml : 0u;
+        load16<true>(sp, n, x);
+        load16<false>(mp - off, k, y);
+        store16(dp, n, x);
+        store16(mp, k, y);
+        if (old) ml = 0;
+    }
+    uint32_t lm = __ballot_sync(kFull, lit > kShort);  // long literal runs: whole-warp copies
+    while (lm) {
+        const int l = __ffs(lm) - 1;
+        lm &= lm - 1;
+        uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(kFull, reinterpret_cast<unsigned long long>(dp), l));
+        const uint8_t* g = reinterpret_cast<const uint8_t*>(__shfl_sync(kFull, reinterpret_cast<unsigned long long>(sp), l));
+        warp_copy<false>(d, g, __shfl_sync(kFull, lit, l), lane);
+    }
+    // ml != 0 from here on means "match still to be copied"
+    for (;;) {
+        const uint32_t pm = __ballot_sync(kFull, ml != 0);
+        if (!pm) break;
+        __syncwarp();
+        const int f = __ffs(pm) - 1;
+        const uint32_t f_md = __shfl_sync(kFull, md, f), f_ml = __shfl_sync(kFull, ml, f), f_off = __shfl_sync(kFull, off, f);
+        if (f_ml > kShort) {  // long match: first in line, whole warp
+            warp_match(lz + f_md, f_off, f_ml, lane);
+            if ((int)lane == f) ml = 0;
+        }
+        const bool go = ml != 0 && ml <= kShort && ((int)lane == f || md - off + ml <= f_md);
+        const bool fast = go && off >= ml;
+        uint32_t x[4];
+        load16<false>(mp - off, fast ? ml : 0u, x);
+        store16(mp, fast ? ml : 0u, x);
+        if (go && !fast) {  // self-overlapping short match: byte-serial
+            const uint8_t* g = mp - off;
+            for (uint32_t b = 0; b < ml; b++) mp[b] = g[b];
+        }
+        if (go) ml = 0;
     }
 }
 
-// Pass 2, one round: matches that read this round's own output and whose source now lies below their slot's frontier.
-template <int NP>
-__device__ __forceinline__ void exec_pass2(WarpShared& ws, uint32_t it, uint32_t lane) {
-    const uint32_t half = lane >> 4, s = lane & 15;
-    Seq e[NP];
-    uint32_t ml[NP], md[NP], c[NP], x[NP][4];
-    uint8_t* dp[NP];
-    bool pd[NP], fs[NP], go[NP], fast[NP];
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
 #pragma unroll
-    for (int q = 0; q < NP; q++) {
-        c[q] = 2 * it + half + 2 * q;
-        e[q] = Seq{0, 0, 0, 0};
-        pd[q] = (ws.pend[c[q]] >> s) & 1;
-        if (pd[q]) e[q] = ws.rec[s * 32 + (c[q] ^ s)];
-        ml[q] = e[q].lens >> 16;
-        md[q] = e[q].dst + (e[q].lens & 0xffffu);
-        fs[q] = pd[q] && s == ws.first[c[q]];
-        dp[q] = reinterpret_cast<uint8_t*>(ws.lz[c[q]]) + md[q];
-        // long matches run when they are first in their slot, with the whole warp
-        uint32_t lm = __ballot_sync(0xffffffffu, fs[q] && ml[q] > kShort);
-        while (lm) {
-            int l = __ffs(lm) - 1;
-            lm &= lm - 1;
-            uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dp[q]), l));
-            warp_match(d, __shfl_sync(0xffffffffu, e[q].off, l), __shfl_sync(0xffffffffu, ml[q], l), lane);
-        }
-        go[q] = pd[q] && ml[q] <= kShort && (fs[q] || md[q] - e[q].off + ml[q] <= ws.frontier[c[q]]);
-        fast[q] = go[q] && e[q].off >= ml[q];
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(kFull, v, d);
+        if ((int)lane >= d) v += t;
     }
-#pragma unroll
-    for (int q = 0; q < NP; q++) load16<false>(dp[q] - e[q].off, fast[q] ? ml[q] : 0u, x[q]);
-#pragma unroll
-    for (int q = 0; q < NP; q++) store16(dp[q], fast[q] ? ml[q] : 0u, x[q]);
-#pragma unroll
-    for (int q = 0; q < NP; q++) {
-        if (go[q] && !fast[q]) {  // self-overlapping short match: byte-serial
-            const uint8_t* g = dp[q] - e[q].off;
-            for (uint32_t b = 0; b < ml[q]; b++) dp[q][b] = g[b];
-        }
-        if (go[q] || (fs[q] && ml[q] > kShort)) atomicAnd(&ws.pend[c[q]], ~(1u << s));
-    }
+    return v;
 }
 
-__global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* __restrict__ comp,
-                                                                 const ChunkDesc* __restrict__ chunks, uint32_t n_chunks,
-                                                                 uint8_t* out, uint8_t* tmp, int32_t* __restrict__ status,
-                                                                 uint32_t* ticket, uint32_t slots) {
-    __shared__ __align__(16) WarpShared s_ws[kWarps];
-    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    WarpShared& ws = s_ws[wid];
+__global__ void __launch_bounds__(32) lz4_decode_kernel(const uint8_t* __restrict__ comp, const ChunkDesc* __restrict__ chunks,
+                                                        uint32_t n_chunks, uint8_t* out, uint8_t* tmp,
+                                                        int32_t* __restrict__ status, uint32_t* ticket, const uint8_t* comp_hi) {
+    __shared__ __align__(16) WarpShared ws;
+    const uint32_t lane = threadIdx.x;
+    const uint8_t* const win = reinterpret_cast<const uint8_t*>(ws.win);
+    uint8_t* const idx8 = reinterpret_cast<uint8_t*>(ws.idx);
 
-    // per-slot (per-lane) parser state
-    int state = lane < slots ? ST_IDLE : ST_EXHAUSTED;
+    // Chunk state.  Warp-uniform: every lane holds the same values and the serial walker runs identically on all
+    // lanes (same cost as running it on one, and nothing has to be broadcast).
+    int state = ST_IDLE;
     uint32_t ci = 0, clen = 0, ulen = 0, scheme = 0;
     const uint8_t* src = nullptr;  // chunk payload
     uint8_t* lz = nullptr;         // where the LZ4 output goes (final position, or the plane buffer for scheme 2)
@@ -300,9 +394,12 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
     uint32_t ip = 0, bend = 0, op = 0, win_lo = 0, blk_op = 0, bmax = 0, fflags = 0;  // fflags: 1 indep, 2 bsum, 4 csum
     uint32_t p_lit = 0, p_lsrc = 0, p_mlen = 0, p_off = 0;
     int err = 0;
+    uintptr_t wbase = 0;        // stream address staged at ws.win[0] (0: none)
+    bool force_serial = false;  // the last speculative round made no progress: one serial round first
+    uint32_t seglim = 32;       // segments per speculative round (fewer where sequences are dense: the record pool is finite)
 
 #ifdef ZG_LZ4_PROFILE
-    long long t_parse = 0, t_p1 = 0, t_p2 = 0, t_fin = 0, n_rounds = 0, n_p2 = 0, tq;
+    long long t_parse = 0, t_res = 0, t_exec = 0, t_serial = 0, n_spec = 0, n_serial = 0, n_true = 0, n_parsed = 0, tq;
 #define ZG_T0() tq = clock64()
 #define ZG_T(acc) do { long long now__ = clock64(); acc += now__ - tq; tq = now__; } while (0)
 #else
@@ -311,119 +408,207 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
 #endif
     for (;;) {
         ZG_T0();
-        // ---- refill idle slots from the ticket counter
-        uint32_t idle = __ballot_sync(0xffffffffu, state == ST_IDLE);
-        if (idle) {
-            uint32_t base = 0;
-            int leader = __ffs(idle) - 1;
-            if ((int)lane == leader) base = atomicAdd(ticket, (uint32_t)__popc(idle));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (state == ST_IDLE) {
-                uint32_t t = base + __popc(idle & ((1u << lane) - 1));
-                if (t < n_chunks) {
-                    const uint32_t k = chunks[t].order;  // longest-first work order (fill_decode_order)
-                    ChunkDesc d = chunks[k < n_chunks ? k : t];
-                    ci = k < n_chunks ? k : t; clen = d.clen; ulen = d.ulen; scheme = d.scheme;
-                    src = comp + d.src_off;
-                    fin_out = out + d.dst_off;
-                    lz = scheme == 2 ? tmp + d.dst_off : fin_out;
-                    ws.src[lane] = reinterpret_cast<unsigned long long>(src);
-                    ws.lz[lane] = reinterpret_cast<unsigned long long>(lz);
-                    ip = 0; op = 0; err = 0; p_lit = p_mlen = 0;
-                    state = ST_START;
-                } else
-                    state = ST_EXHAUSTED;
-            }
+        if (state == ST_IDLE) {
+            uint32_t t = 0;
+            if (lane == 0) t = atomicAdd(ticket, 1u);
+            t = __shfl_sync(kFull, t, 0);
+            if (t >= n_chunks) break;
+            const uint32_t k = chunks[t].order;  // longest-first work order (fill_decode_order)
+            ci = k < n_chunks ? k : t;
+            const ChunkDesc d = chunks[ci];
+            clen = d.clen; ulen = d.ulen; scheme = d.scheme;
+            src = comp + d.src_off;
+            fin_out = out + d.dst_off;
+            lz = scheme == 2 ? tmp + d.dst_off : fin_out;
+            ip = 0; op = 0; err = 0; p_lit = p_mlen = 0;
+            force_serial = false;
+            seglim = 32;
+            state = ST_START;
         }
-        if (__all_sync(0xffffffffu, state == ST_EXHAUSTED)) break;
 
-        // ---- parse: every active lane appends up to kSeqCap records for its own chunk
-        uint32_t cnt = 0, pmask = 0;
-        ws.w0[lane] = op;
-        bool finished = false;  // chunk complete (ok or error) after this round's records
-        // Lock-step matters: lanes execute together only while they follow the same path, and a lane that falls behind
-        // would otherwise finish its quota alone.  So the loop runs a fixed number of steps for the whole warp and every
-        // active lane makes ONE step per iteration -- normally one sequence on the hot path; block/frame boundaries,
-        // length-extension bytes, oversized pieces and errors take the general path of that iteration and rejoin.
-        uint32_t wv0 = 0, wv1 = 0, wv2 = 0, wip = 0xffffffffu;  // raw words of the 8-byte window at position wip
+        if (state == ST_IN_BLOCK && (p_lit | p_mlen) == 0 && !force_serial && bend - ip >= kSpecMin) {
+            // ================= speculative round =================
+            const uint32_t nseg = min(seglim, (bend - ip + kSeg - 1) / kSeg);  // the last segment may be short
+            const uint32_t spanend = min(ip + nseg * kSeg, bend);
+            const uintptr_t a0 = reinterpret_cast<uintptr_t>(src) + ip;
+            if (wbase != (a0 & ~(uintptr_t)15)) {
+                cp_async_wait_all();  // a request for another position may still be in flight
+                wbase = a0 & ~(uintptr_t)15;
+                stage_window(ws, wbase, comp_hi, lane);
+            }
+            const uint32_t wofs = (uint32_t)(a0 - wbase) - ip;
+            cp_async_wait_all();
+            __syncwarp();
+
+            // ---- parse: lane k walks segment k
+            uint32_t pos = ip + lane * kSeg, cnt = 0;
+            uint32_t used = 0;  // pool slots handed out (uniform; may run past kPool, the excess is not stored)
+            const uint32_t lt = (1u << lane) - 1;
+            const uint32_t segend = min(pos + kSeg, spanend);
+            bool run = lane < nseg;  // chain alive (not stopped by something unusual)
 #pragma unroll 1
-        for (int step = 0; step < kSeqCap; step++) {
-            const bool act = !finished && state != ST_IDLE && state != ST_EXHAUSTED && cnt < (uint32_t)kSeqCap;
-            if (!__any_sync(0xffffffffu, act)) break;
-            if (!act) continue;
-            bool handled = false;
-            if (state == ST_IN_BLOCK && (p_lit | p_mlen) == 0 && bend - ip >= 48 && ulen - op >= 40) {
-                // Hot path: far from the end of the block and of the output.  If there are no length-extension bytes the
-                // only checks left of the oracle's list are those on the offset; the rest is implied by the two margins
-                // (such a sequence consumes <= 17 input bytes and produces <= 32 output bytes).  Software-pipelined: the
-                // serial chain is window -> token -> literal length -> next position -> next window, so the next
-                // window's words are requested as soon as the literal length is known, carried RAW into the next step,
-                // and the record bookkeeping runs in the shadow of that load.
-                const uintptr_t a = reinterpret_cast<uintptr_t>(src + ip);
-                if (wip != ip) {
-                    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-                    wv0 = __ldg(w); wv1 = __ldg(w + 1); wv2 = __ldg(w + 2);
+            for (uint32_t it = 0; it < kCap; it++) {
+                const bool act = run && pos < segend;
+                if (!__any_sync(kFull, act)) break;
+                Hop h;
+                h.ok = false;
+                if (act) {
+                    h = spec_hop(src, win, wofs, pos, bend);
+                    if (!h.ok) run = false;
                 }
-                const uint32_t sh0 = (uint32_t)(a & 3) * 8;
-                const uint32_t lo = __funnelshift_r(wv0, wv1, sh0), hi = __funnelshift_r(wv1, wv2, sh0);
-                const uint64_t w64 = ((uint64_t)hi << 32) | lo;
-                const uint32_t tok = lo & 0xffu;
-                const uint32_t lit = tok >> 4, mln = tok & 15u;
-                if (lit != 15u && mln != 15u) {
-                    // A second sequence that lies wholly inside the same 8-byte window (literal runs of 0-2 bytes are
-                    // the common case on both text and byte-grouped bf16) is taken in the same step: one load round
-                    // trip then yields two records.
-                    const uint32_t k1 = 3 + lit;
-                    uint32_t lit2 = 0, mln2 = 0, off2 = 0;
-                    bool two = false;
-                    if (k1 <= 5 && cnt + 2 <= (uint32_t)kSeqCap && ulen - op >= 72) {
-                        const uint32_t r = (uint32_t)(w64 >> (8 * k1));
-                        lit2 = (r >> 4) & 15u; mln2 = r & 15u;
-                        if (lit2 + k1 <= 5 && mln2 != 15u) {
-                            two = true;
-                            off2 = (uint32_t)(w64 >> (8 * (k1 + 1 + lit2))) & 0xffffu;
-                        }
-                    }
-                    const uint32_t nip = ip + k1 + (two ? 3 + lit2 : 0u);
-                    const uint32_t* nw = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(src + nip) & ~(uintptr_t)3);
-                    const uint32_t n0 = __ldg(nw), n1 = __ldg(nw + 1), n2 = __ldg(nw + 2);
-                    uint32_t off;
-                    if (lit <= 5) off = (uint32_t)(w64 >> (8 + 8 * lit)) & 0xffffu;
-                    else off = rd8(src + ip + 1 + lit) | (rd8(src + ip + 2 + lit) << 8);
-                    const uint32_t vop = op + lit, ml = mln + 4;
-                    if (off == 0 || off > vop - win_lo) { err = E_LZ4_BLOCK; finished = true; }
-                    else {
-                        Seq e{ip + 1, op, lit | (ml << 16), off};
-                        ws.rec[cnt * 32 + (lane ^ cnt)] = e;
-                        pmask |= 1u << cnt;
+                const uint32_t m = __ballot_sync(kFull, h.ok);
+                const uint32_t slot = used + __popc(m & lt);
+                used += __popc(m);
+                if (h.ok) {
+                    if (slot < kPool) {
+                        ws.pool[slot] = make_uint2((pos - ip) | (h.lit << 16), h.ml | (h.off << 16));
+                        ws.meta[slot] = (uint16_t)((lane << 8) | cnt);
+                        idx8[pos - ip] = (uint8_t)(cnt + 1);
                         cnt++;
-                        op = vop + ml;
-                        if (two) {
-                            const uint32_t vop2 = op + lit2, ml2 = mln2 + 4;
-                            if (off2 == 0 || off2 > vop2 - win_lo) { err = E_LZ4_BLOCK; finished = true; }
-                            else {
-                                Seq e2{ip + k1 + 1, op, lit2 | (ml2 << 16), off2};
-                                ws.rec[cnt * 32 + (lane ^ cnt)] = e2;
-                                pmask |= 1u << cnt;
-                                cnt++;
-                                op = vop2 + ml2;
-                            }
-                        }
-                        if (!finished) { ip = nip; wv0 = n0; wv1 = n1; wv2 = n2; wip = nip; }
-                    }
-                    handled = true;
+                        pos = h.nip;
+                    } else
+                        run = false;  // pool exhausted: the chain stops here
                 }
             }
-            if (handled) continue;
-            wip = 0xffffffffu;
+            __syncwarp();
+            // ---- join: walk on into the following segments until a position their own chain visited
+            uint32_t nxt = 32, nj = 0;
+            bool seek = run && pos >= segend && pos < spanend;
+#pragma unroll 1
+            for (uint32_t e = 0; e <= kJoinHops; e++) {
+                if (!__any_sync(kFull, seek)) break;
+                Hop h;
+                h.ok = false;
+                if (seek) {
+                    const uint32_t j = idx8[pos - ip];
+                    if (j) { nxt = (pos - ip) / kSeg; nj = j - 1; seek = false; }
+                    else if (e == kJoinHops || used >= kPool) seek = false;  // the round ends at pos
+                    else {
+                        h = spec_hop(src, win, wofs, pos, bend);
+                        if (!h.ok) run = seek = false;
+                    }
+                }
+                const uint32_t m = __ballot_sync(kFull, h.ok);
+                const uint32_t slot = used + __popc(m & lt);
+                used += __popc(m);
+                if (h.ok) {
+                    if (slot < kPool) {
+                        ws.pool[slot] = make_uint2((pos - ip) | (h.lit << 16), h.ml | (h.off << 16));
+                        ws.meta[slot] = (uint16_t)((lane << 8) | cnt);
+                        cnt++;
+                        pos = h.nip;
+                        if (pos >= spanend) seek = false;
+                    } else
+                        seek = false;
+                }
+            }
+            // the next round takes fewer segments when this one ran out of record slots, more when it used few
+            if (used > kPool) seglim = seglim > 12 ? seglim - 8 : 4;
+            else if (used < kPool * 5 / 8 && seglim < 32) seglim += 4;
+            ZG_T(t_parse);
+#ifdef ZG_LZ4_PROFILE
+            n_parsed += __reduce_add_sync(kFull, cnt);
+#endif
+            // ---- resolve: which lanes lie on the chain that starts at lane 0
+            uint32_t jump = nxt, reach = 1u << lane;
+#pragma unroll
+            for (int d = 0; d < 5; d++) {
+                const uint32_t jr = __shfl_sync(kFull, reach, jump & 31), jj = __shfl_sync(kFull, jump, jump & 31);
+                if (jump < 32) { reach |= jr; jump = jj; }
+            }
+            const uint32_t truemask = __shfl_sync(kFull, reach, 0);
+            const bool istrue = (truemask >> lane) & 1;
+            if (istrue && nxt < 32) ws.sj[nxt] = nj;
+            __syncwarp();
+            const uint32_t first = (istrue && lane != 0) ? ws.sj[lane] : 0u;
+            const uint32_t tc = istrue ? cnt - first : 0u;
+            const uint32_t incl = warp_incl_scan(tc, lane);
+            const uint32_t T = __shfl_sync(kFull, incl, 31);
+            ws.first[lane] = first;
+            ws.base[lane] = istrue ? (int32_t)(incl - tc) - (int32_t)first : kNotTrue;
+            __syncwarp();
+            const uint32_t nrec = min(used, kPool);
+#pragma unroll 1
+            for (uint32_t sl = lane; sl < nrec; sl += 32) {
+                const uint32_t mt = ws.meta[sl], k = mt >> 8, q = mt & 255u;
+                const int32_t b = ws.base[k];
+                if (b != kNotTrue && q >= ws.first[k]) ws.ref[b + (int32_t)q] = (uint16_t)sl;
+            }
+            const uint32_t next_ip = __shfl_sync(kFull, pos, 31 - __clz(truemask));
+            __syncwarp();
+            // the window and the position map are dead from here: request the next round's now
+            const bool stopped = !__shfl_sync(kFull, run, 31 - __clz(truemask));  // the true chain met something unusual
+            if (T != 0 && !stopped && bend - next_ip >= kSpecMin) {
+                wbase = (reinterpret_cast<uintptr_t>(src) + next_ip) & ~(uintptr_t)15;
+                stage_window(ws, wbase, comp_hi, lane);
+            }
+            ZG_T(t_res);
+
+            // ---- execute: 32 consecutive true sequences per step
+            const uint32_t ip0 = ip;
+            uint32_t gop = op;
+            bool bad = false;
+#pragma unroll 1
+            for (uint32_t g0 = 0; g0 < T && !bad; g0 += 32) {
+                const uint32_t r = g0 + lane;
+                uint32_t prel = 0, lit = 0, ml = 0, off = 0;
+                if (r < T) {
+                    const uint2 rec = ws.pool[ws.ref[r]];
+                    prel = rec.x & 0xffffu; lit = rec.x >> 16; ml = rec.y & 0xffffu; off = rec.y >> 16;
+                }
+                const uint32_t len = lit + ml;
+                const uint32_t sc = warp_incl_scan(len, lane);
+                const uint32_t dst = gop + sc - len;
+                // the oracle's checks that need output positions; a failing sequence goes to the serial walker
+                const bool anomaly = r < T && (off > dst + lit - win_lo || dst + len > ulen);
+                const uint32_t am = __ballot_sync(kFull, anomaly);
+                uint32_t adv = __shfl_sync(kFull, sc, 31);
+                if (am) {
+                    const int fa = __ffs(am) - 1;
+                    bad = true;
+                    ip = ip0 + __shfl_sync(kFull, prel, fa);  // resume in front of that sequence
+                    adv = __shfl_sync(kFull, dst, fa) - gop;
+                    if ((int)lane >= fa) lit = ml = 0;
+                }
+                // literals follow the token and the length-extension bytes (one per 255, plus the closing one)
+                const uint32_t lit_src = ip0 + prel + 1 + (lit >= 15u ? (lit - 15u) / 255u + 1u : 0u);
+                exec_group(src, lz, gop, lit_src, lit, ml, off, dst, lane);
+                gop += adv;
+#ifdef ZG_LZ4_PROFILE
+                n_true += __popc(__ballot_sync(kFull, (lit | ml) != 0));
+#endif
+            }
+            op = gop;
+            if (!bad) ip = next_ip;
+            if (bad || T == 0 || stopped) force_serial = true;
+            ZG_T(t_exec);
+#ifdef ZG_LZ4_PROFILE
+            n_spec++;
+#endif
+            continue;
+        }
+
+        // ================= serial round: up to kSerialCap sequences, every check of the oracle in its order =================
+        uint32_t cnt = 0;
+        const uint32_t op_start = op;
+        bool finished = false;  // chunk complete (ok or error) after this round's records
+        force_serial = false;
+#define ZG_EMIT(LSRC, LIT, ML, OFF)                                                                  \
+    do {                                                                                             \
+        if (lane == 0) {                                                                             \
+            ws.srec[3 * cnt] = (LSRC); ws.srec[3 * cnt + 1] = (LIT) | ((ML) << 16); ws.srec[3 * cnt + 2] = (OFF); \
+        }                                                                                            \
+        cnt++;                                                                                       \
+    } while (0)
+#pragma unroll 1
+        for (uint32_t step = 0; step < kSerialCap && !finished && cnt < kSerialCap; step++) {
             if (state == ST_IN_BLOCK && (p_lit | p_mlen) == 0) {
-                // One sequence.  The checks and their order are those of the oracle's lz4_block; the bytes come from
-                // an 8-byte window fetched with one round trip (token, short literal run and offset usually all sit
-                // inside it).
+                // One sequence.  The bytes come from an 8-byte window fetched with one round trip (token, short
+                // literal run and offset usually all sit inside it).
                 if (ip >= bend) { err = E_LZ4_BLOCK; finished = true; continue; }
                 const uint32_t ip0 = ip;
-                const uint64_t win = load_window(src + ip0);
-                const uint32_t tok = (uint32_t)win & 0xffu;
+                const uint64_t w8 = load_window(src + ip0);
+                const uint32_t tok = (uint32_t)w8 & 0xffu;
                 ip++;
                 uint32_t lit = tok >> 4;
                 bool bad = false;
@@ -447,7 +632,7 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                 if (bend - ip < 2) { err = E_LZ4_BLOCK; finished = true; continue; }
                 const uint32_t rel = ip - ip0;
                 uint32_t off;
-                if (rel <= 6) off = (uint32_t)(win >> (8 * rel)) & 0xffffu;
+                if (rel <= 6) off = (uint32_t)(w8 >> (8 * rel)) & 0xffffu;
                 else off = rd8(src + ip) | (rd8(src + ip + 1) << 8);
                 ip += 2;
                 uint32_t ml = tok & 15;
@@ -465,10 +650,7 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                 if (off == 0 || off > vop - win_lo) { err = E_LZ4_BLOCK; finished = true; continue; }
                 if (ml > ulen - vop) { err = E_SIZE_MISMATCH; finished = true; continue; }
                 if (lit <= kMaxPiece && ml <= kMaxPiece) {
-                    Seq e{lsrc, op, lit | (ml << 16), off};
-                    ws.rec[cnt * 32 + (lane ^ cnt)] = e;
-                    pmask |= 1u << cnt;
-                    cnt++;
+                    ZG_EMIT(lsrc, lit, ml, off);
                     op = vop + ml;
                 } else {
                     p_lit = lit; p_lsrc = lsrc; p_mlen = ml; p_off = off;  // split into pieces below
@@ -476,12 +658,9 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                 continue;
             }
             if (p_lit | p_mlen) {
-                uint32_t l = p_lit < kMaxPiece ? p_lit : kMaxPiece;
-                uint32_t m = (l == p_lit) ? (p_mlen < kMaxPiece ? p_mlen : kMaxPiece) : 0u;
-                Seq e{p_lsrc, op, l | (m << 16), p_off};
-                ws.rec[cnt * 32 + (lane ^ cnt)] = e;
-                if (m) pmask |= 1u << cnt;
-                cnt++;
+                const uint32_t l = p_lit < kMaxPiece ? p_lit : kMaxPiece;
+                const uint32_t m = (l == p_lit) ? (p_mlen < kMaxPiece ? p_mlen : kMaxPiece) : 0u;
+                ZG_EMIT(p_lsrc, l, m, p_off);
                 op += l + m; p_lsrc += l; p_lit -= l; p_mlen -= m;
                 continue;
             }
@@ -536,6 +715,8 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                         win_lo = (fflags & 1) ? op : 0u;
                         bend = ip + bs;
                         state = ST_IN_BLOCK;
+                        // leave the round here when the block is long enough for the speculative walk
+                        if (bs >= kSpecMin) step = kSerialCap;
                     }
                     break;
                 }
@@ -552,81 +733,42 @@ __global__ void __launch_bounds__(kWarps * 32) lz4_decode_kernel(const uint8_t* 
                 default: finished = true; break;
             }
         }
-        ws.cnt[lane] = (uint8_t)cnt;
-        ws.pend[lane] = pmask;
+#undef ZG_EMIT
         __syncwarp();
-        ZG_T(t_parse);
-        const uint32_t have = __ballot_sync(0xffffffffu, cnt > 0);  // slots with records this round
-
-        // ---- execute, pass 1: every literal run, and every match whose source lies wholly before this round's
-        // output (no dependence on anything written this round: ~91 % of matches on text, ~98 % on byte-grouped bf16)
-#pragma unroll 1
-        for (uint32_t it = 0; it < 16; it += 2) {
-            const uint32_t m4 = (have >> (2 * it)) & 0xfu;
-            if (m4 == 0) continue;
-            if (m4 >> 2) exec_pass1<2>(ws, it, lane);
-            else exec_pass1<1>(ws, it, lane);
-        }
-        __syncwarp();
-        ZG_T(t_p1);
-
-        // ---- execute, pass 2: the matches that read this round's own output.  Per slot they are ordered; a match may
-        // run as soon as its source lies below the slot's frontier (start of the first match still pending), so every
-        // round retires at least one match per slot and usually most of them.
-        for (;;) {
-            uint32_t p = ws.pend[lane];
-            if (p) {
-                uint32_t f = (uint32_t)__ffs(p) - 1;
-                Seq e = ws.rec[f * 32 + (lane ^ f)];
-                ws.first[lane] = (uint8_t)f;
-                ws.frontier[lane] = e.dst + (e.lens & 0xffffu);
+        {
+            uint32_t lit_src = 0, lit = 0, ml = 0, off = 0;
+            if (lane < cnt) {
+                lit_src = ws.srec[3 * lane];
+                const uint32_t lens = ws.srec[3 * lane + 1];
+                lit = lens & 0xffffu; ml = lens >> 16;
+                off = ws.srec[3 * lane + 2];
             }
-            const uint32_t anyp = __ballot_sync(0xffffffffu, p != 0);
-            if (!anyp) break;
-            __syncwarp();
+            if (cnt) {  // uniform
+                const uint32_t len = lit + ml;
+                const uint32_t sc = warp_incl_scan(len, lane);
+                exec_group(src, lz, op_start, lit_src, lit, ml, off, op_start + sc - len, lane);
+                __syncwarp();  // srec is rewritten next round
+            }
+        }
+        ZG_T(t_serial);
 #ifdef ZG_LZ4_PROFILE
-            n_p2++;
+        n_serial++;
 #endif
-#pragma unroll 1
-            for (uint32_t it = 0; it < 16; it += 2) {
-                const uint32_t m4 = (anyp >> (2 * it)) & 0xfu;
-                if (m4 == 0) continue;
-                if (m4 >> 2) exec_pass2<2>(ws, it, lane);
-                else exec_pass2<1>(ws, it, lane);
-            }
-            __syncwarp();
-        }
-
-        ZG_T(t_p2);
-        // ---- chunks that finished this round: regroup (scheme 2) and publish the status
-        uint32_t fin = __ballot_sync(0xffffffffu, finished);
-        while (fin) {
-            int c = __ffs(fin) - 1;
-            fin &= fin - 1;
-            int c_err = __shfl_sync(0xffffffffu, err, c);
-            uint32_t c_scheme = __shfl_sync(0xffffffffu, scheme, c);
-            if (c_err == 0 && c_scheme == 2) {
-                uint8_t* c_out = reinterpret_cast<uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(fin_out), c));
-                const uint8_t* c_lz = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(lz), c));
-                warp_regroup(c_out, c_lz, __shfl_sync(0xffffffffu, ulen, c), lane);
-            }
-        }
+        // ---- chunk finished this round: regroup (scheme 2) and publish the status
         if (finished) {
-            status[ci] = err;
+            __syncwarp();
+            if (err == 0 && scheme == 2) warp_regroup(fin_out, lz, ulen, lane);
+            if (lane == 0) status[ci] = err;
             state = ST_IDLE;
         }
-        __syncwarp();
-        ZG_T(t_fin);
-#ifdef ZG_LZ4_PROFILE
-        n_rounds++;
-#endif
     }
 #ifdef ZG_LZ4_PROFILE
     if (lane == 0) {
         unsigned long long* pr = reinterpret_cast<unsigned long long*>(ticket) + 2;
-        atomicAdd(pr + 0, (unsigned long long)t_parse); atomicAdd(pr + 1, (unsigned long long)t_p1);
-        atomicAdd(pr + 2, (unsigned long long)t_p2); atomicAdd(pr + 3, (unsigned long long)t_fin);
-        atomicAdd(pr + 4, (unsigned long long)n_rounds); atomicAdd(pr + 5, (unsigned long long)n_p2);
+        atomicAdd(pr + 0, (unsigned long long)t_parse); atomicAdd(pr + 1, (unsigned long long)t_res);
+        atomicAdd(pr + 2, (unsigned long long)t_exec); atomicAdd(pr + 3, (unsigned long long)t_serial);
+        atomicAdd(pr + 4, (unsigned long long)n_spec); atomicAdd(pr + 5, (unsigned long long)n_serial);
+        atomicAdd(pr + 6, (unsigned long long)n_true); atomicAdd(pr + 7, (unsigned long long)n_parsed);
     }
 #endif
 }
@@ -649,7 +791,6 @@ size_t decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes) {
 
 cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkDesc* chunks, size_t n, uint8_t* out,
                           uint64_t out_bytes, int32_t* status, void* scratch, size_t scratch_bytes, cudaStream_t st) {
-    (void)comp_bytes;
     if (n == 0) return cudaSuccess;
     if (scratch_bytes < decode_scratch_bytes(n, out_bytes) || n >= 0xffffffffull) return cudaErrorInvalidValue;
     uint8_t* sb = static_cast<uint8_t*>(scratch);
@@ -657,25 +798,13 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     uint8_t* tmp = sb + 256;
     cudaError_t e = cudaMemsetAsync(ticket, 0, 256, st);
     if (e != cudaSuccess) return e;
-    // Slots (chunks in flight) per warp: few when the batch is small, so that every SM gets many warps (the token walk
-    // and the copy rounds are latency chains; only other warps hide them); up to 32 for large batches, where the
-    // serial token walk is then spread over all lanes.  Chunks are handed out longest-first through the ticket
-    // counter, and for batches larger than the machine the launch keeps about half as many slots as chunks: a slot
-    // that finishes a long chunk picks up a short one, so the tail stays balanced.  Measured on B200 (profiles/): 8.5k text chunks -> 2 slots, 15.7k
-    // bf16 chunks -> 4 slots.  ZEST_LZ4_SLOTS / ZEST_LZ4_WARPS / ZEST_LZ4_OVERSUB override (tuning knobs).
-    size_t want_warps = 148 * 16, max_warps = 148 * 24;
-    size_t oversub = n > max_warps ? 2 : 1;  // a batch that fits the machine at one chunk per slot runs at single-chunk latency
-    if (const char* e = getenv("ZEST_LZ4_WARPS")) { long v = atol(e); if (v > 0) want_warps = max_warps = (size_t)v; }
-    if (const char* e = getenv("ZEST_LZ4_OVERSUB")) { long v = atol(e); if (v > 0) oversub = (size_t)v; }
-    uint32_t slots = (uint32_t)((n + want_warps * oversub - 1) / (want_warps * oversub));
-    if (const char* e = getenv("ZEST_LZ4_SLOTS")) { long v = atol(e); if (v > 0) slots = (uint32_t)v; }
-    if (slots < 1) slots = 1;
-    if (slots > 32) slots = 32;
-    size_t warps = (n + slots * oversub - 1) / (slots * oversub);
-    if (warps > max_warps) warps = max_warps;
-    if (warps < 1) warps = 1;
-    unsigned blocks = (unsigned)((warps + kWarps - 1) / kWarps);
-    lz4_decode_kernel<<<blocks, kWarps * 32, 0, st>>>(comp, chunks, (uint32_t)n, out, tmp, status, ticket, slots);
+    // One warp per CTA, one chunk per warp at a time; the grid is what the machine keeps resident (shared memory
+    // allows 15 CTAs per SM) and the ticket counter feeds it, longest chunks first.  ZEST_LZ4_WARPS overrides.
+    size_t warps = 148 * 15;
+    if (const char* v = getenv("ZEST_LZ4_WARPS")) { long w = atol(v); if (w > 0) warps = (size_t)w; }
+    if (warps > n) warps = n;
+    const uint8_t* comp_hi = comp + align_up((size_t)comp_bytes, 16);
+    lz4_decode_kernel<<<(unsigned)warps, 32, 0, st>>>(comp, chunks, (uint32_t)n, out, tmp, status, ticket, comp_hi);
     return cudaGetLastError();
 }
 
