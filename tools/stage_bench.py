@@ -123,9 +123,9 @@ def main():
             ms = timed(k_decode, args.steps)
             if os.environ.get("ZG_PROF"):
                 k_decode(); torch.cuda.synchronize()
-                pr = s_dec[16:80].cpu().numpy().view(np.uint64)
+                pr = s_dec[16:88].cpu().numpy().view(np.uint64)
                 tot = float(pr[:4].sum()) or 1.0
-                print(f"      phase cycles: parse {pr[0]/tot:.3f} resolve {pr[1]/tot:.3f} execute {pr[2]/tot:.3f} serial {pr[3]/tot:.3f}  spec rounds {pr[4]} serial rounds {pr[5]}  true records {pr[6]} parsed records {pr[7]}  total warp-cycles {tot:.3e}")
+                print(f"      phase cycles: parse {pr[0]/tot:.3f} resolve {pr[1]/tot:.3f} execute {pr[2]/tot:.3f} serial {pr[3]/tot:.3f}  spec rounds {pr[4]} serial rounds {pr[5]}  true records {pr[6]} parsed records {pr[7]} pending matches {pr[8]}  total warp-cycles {tot:.3e}")
             print(f"decode slots={s or 'auto':>4} warps={w or 'auto':>5} oversub={ov or 'auto':>2}: {ms:8.3f} ms  {total/ms/1e6:8.1f} GB/s uncompressed  {(total+comp_bytes)/ms/1e6:8.1f} GB/s alg  parity={'ok' if ok else 'FAIL'}", flush=True)
             res[f"decode_s{s}_w{w}"] = ms
     os.environ.pop("ZEST_LZ4_SLOTS", None); os.environ.pop("ZEST_LZ4_WARPS", None)

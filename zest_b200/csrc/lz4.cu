@@ -48,6 +48,10 @@ namespace {
 constexpr uint32_t kFull = 0xffffffffu;
 constexpr uint32_t kShort = 16;       // literal runs / matches up to this length are copied by their own lane
 constexpr uint32_t kMaxPiece = 65535;
+#ifndef ZG_NP
+#define ZG_NP 1
+#endif
+constexpr int kNP = ZG_NP;            // groups of 32 sequences per execute step
 constexpr uint32_t kSerialCap = 16;   // sequences per round of the serial walker
 constexpr uint32_t kSeg = 68;         // speculative segment, stream bytes: 17 words, so 32 lanes start in 32 banks
 constexpr uint32_t kCap = 24;         // a 68-byte segment holds at most 23 sequences
@@ -61,11 +65,10 @@ constexpr uint32_t kSpecMin = 32;     // blocks (or block remainders) shorter th
 enum : int { ST_IDLE = 0, ST_START, ST_BLOCK_HDR, ST_IN_BLOCK, ST_AFTER_BLOCK, ST_FINISH, ST_EXHAUSTED };
 
 struct WarpShared {
-    uint4 win[kWinBytes / 16];       // staged stream window
-    uint4 idx[kSpanMax / 16];        // byte map over the span: 1 + record index of the home chain at that byte, else 0
+    uint4 win[kWinBytes / 16];       // staged stream window; after the walk: true records in stream order (pool slots)
+    uint32_t bmp[kSpanMax / 32];     // bit map over the span: positions visited by the chain of the segment they lie in
     uint2 pool[kPool];               // records of the round: {pos - ip | lit << 16, ml | off << 16}
     uint16_t meta[kPool];            // per record: lane << 8 | number of the record within its lane's chain
-    uint16_t ref[kPool];             // true records in stream order: pool slot
     uint32_t sj[32];                 // per lane: number of its first true record, posted by the chain that joins it
     uint32_t first[32];              // per lane: the same, for everyone to read
     int32_t base[32];                // per lane: stream-order index of its record number 0 (kNotTrue: lane not true)
@@ -222,7 +225,7 @@ __device__ __forceinline__ void stage_window(WarpShared& ws, uintptr_t A, const 
     for (uint32_t i = lane; i < kWinBytes / 16; i += 32)
         if (g + 16 * i + 16 <= comp_hi) cp_async16(&ws.win[i], g + 16 * i);
 #pragma unroll
-    for (uint32_t i = lane; i < kSpanMax / 16; i += 32) ws.idx[i] = make_uint4(0, 0, 0, 0);
+    for (uint32_t i = lane; i < kSpanMax / 32; i += 32) ws.bmp[i] = 0;
 }
 
 // One speculative hop: the sequence whose token sits at stream position pos (relative to the chunk payload).
@@ -312,38 +315,12 @@ __device__ __noinline__ Hop spec_hop_general(const uint8_t* src, const uint8_t* 
     return h;
 }
 
-// One execute step: up to 32 consecutive sequences of one chunk in stream order, one per lane (lanes without a
-// sequence pass lit = ml = 0).  dst is the sequence's output position, op0 the position of the step's first byte;
-// everything below op0 is final.  Pass 1 copies every literal run and every match whose source lies wholly below
-// op0 (most of them); the rest wait for the frontier -- the start of the lowest match still pending, below which
-// all bytes are final -- and usually go in one or two more rounds.
-__device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint32_t op0, uint32_t lit_src, uint32_t lit,
-                                           uint32_t ml, uint32_t off, uint32_t dst, uint32_t lane) {
-    __syncwarp();
-    const uint8_t* sp = src + lit_src;
-    uint8_t* dp = lz + dst;
-    const uint32_t md = dst + lit;  // where the match goes
+// The matches of up to 32 consecutive sequences (one per lane, stream order, ml = 0: none) whose sources may lie
+// in the output of those same sequences.  Everything below the first of them is final.  Each round copies the
+// first pending match and every other one whose source ends below it -- the frontier, below which all bytes are
+// final -- so most steps finish in one or two rounds.
+__device__ __forceinline__ void match_rounds(uint8_t* lz, uint32_t md, uint32_t ml, uint32_t off, uint32_t lane) {
     uint8_t* mp = lz + md;
-    {
-        uint32_t x[4], y[4];
-        const uint32_t n = lit <= kShort ? lit : 0u;
-        const bool old = ml != 0 && ml <= kShort && md - off + ml <= op0;
-        const uint32_t k = old ? ml : 0u;
-        load16<true>(sp, n, x);
-        load16<false>(mp - off, k, y);
-        store16(dp, n, x);
-        store16(mp, k, y);
-        if (old) ml = 0;
-    }
-    uint32_t lm = __ballot_sync(kFull, lit > kShort);  // long literal runs: whole-warp copies
-    while (lm) {
-        const int l = __ffs(lm) - 1;
-        lm &= lm - 1;
-        uint8_t* d = reinterpret_cast<uint8_t*>(__shfl_sync(kFull, reinterpret_cast<unsigned long long>(dp), l));
-        const uint8_t* g = reinterpret_cast<const uint8_t*>(__shfl_sync(kFull, reinterpret_cast<unsigned long long>(sp), l));
-        warp_copy<false>(d, g, __shfl_sync(kFull, lit, l), lane);
-    }
-    // ml != 0 from here on means "match still to be copied"
     for (;;) {
         const uint32_t pm = __ballot_sync(kFull, ml != 0);
         if (!pm) break;
@@ -367,6 +344,55 @@ __device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint
     }
 }
 
+// One execute step: NP x 32 consecutive sequences of one chunk in stream order, lane l holding sequences l, 32 + l, ...
+// (lanes without a sequence pass lit = ml = 0).  dst is the sequence's output position, op0 the position of the
+// step's first byte; everything below op0 is final.  Pass 1 copies every literal run and every match whose source
+// lies wholly below op0 (most of them) with all loads of the step in flight together; the matches that read the
+// step's own output follow, 32 at a time, in frontier rounds.
+template <int NP>
+__device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint32_t op0, const uint32_t (&lit_src)[NP],
+                                           const uint32_t (&lit)[NP], uint32_t (&ml)[NP], const uint32_t (&off)[NP],
+                                           const uint32_t (&dst)[NP], uint32_t lane) {
+    __syncwarp();
+    uint32_t x[NP][4], y[NP][4], n[NP], k[NP];
+    bool old[NP];
+#pragma unroll
+    for (int q = 0; q < NP; q++) {
+        const uint32_t md = dst[q] + lit[q];  // where the match goes
+        n[q] = lit[q] <= kShort ? lit[q] : 0u;
+        old[q] = ml[q] != 0 && md - off[q] + ml[q] <= op0;
+        k[q] = (old[q] && ml[q] <= kShort) ? ml[q] : 0u;
+    }
+#pragma unroll
+    for (int q = 0; q < NP; q++) load16<true>(src + lit_src[q], n[q], x[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) load16<false>(lz + dst[q] + lit[q] - off[q], k[q], y[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) store16(lz + dst[q], n[q], x[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) store16(lz + dst[q] + lit[q], k[q], y[q]);
+#pragma unroll
+    for (int q = 0; q < NP; q++) {
+        uint32_t lm = __ballot_sync(kFull, lit[q] > kShort);  // long literal runs: whole-warp copies
+        while (lm) {
+            const int l = __ffs(lm) - 1;
+            lm &= lm - 1;
+            warp_copy<false>(lz + __shfl_sync(kFull, dst[q], l), src + __shfl_sync(kFull, lit_src[q], l),
+                             __shfl_sync(kFull, lit[q], l), lane);
+        }
+        lm = __ballot_sync(kFull, old[q] && ml[q] > kShort);  // long matches from below the step: the same
+        while (lm) {
+            const int l = __ffs(lm) - 1;
+            lm &= lm - 1;
+            const uint32_t m_md = __shfl_sync(kFull, dst[q] + lit[q], l);
+            warp_copy<true>(lz + m_md, lz + m_md - __shfl_sync(kFull, off[q], l), __shfl_sync(kFull, ml[q], l), lane);
+        }
+        if (old[q]) ml[q] = 0;
+    }
+#pragma unroll
+    for (int q = 0; q < NP; q++) match_rounds(lz, dst[q] + lit[q], ml[q], off[q], lane);
+}
+
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -376,13 +402,14 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
     return v;
 }
 
-__global__ void __launch_bounds__(32) lz4_decode_kernel(const uint8_t* __restrict__ comp, const ChunkDesc* __restrict__ chunks,
+__global__ void __launch_bounds__(32, 20) lz4_decode_kernel(const uint8_t* __restrict__ comp, const ChunkDesc* __restrict__ chunks,
                                                         uint32_t n_chunks, uint8_t* out, uint8_t* tmp,
                                                         int32_t* __restrict__ status, uint32_t* ticket, const uint8_t* comp_hi) {
     __shared__ __align__(16) WarpShared ws;
     const uint32_t lane = threadIdx.x;
     const uint8_t* const win = reinterpret_cast<const uint8_t*>(ws.win);
-    uint8_t* const idx8 = reinterpret_cast<uint8_t*>(ws.idx);
+    uint16_t* const ref = reinterpret_cast<uint16_t*>(ws.win);  // the window is dead once the walk is over
+    static_assert(kPool * 2 <= kWinBytes, "stream-order list must fit the window");
 
     // Chunk state.  Warp-uniform: every lane holds the same values and the serial walker runs identically on all
     // lanes (same cost as running it on one, and nothing has to be broadcast).
@@ -394,7 +421,6 @@ __global__ void __launch_bounds__(32) lz4_decode_kernel(const uint8_t* __restric
     uint32_t ip = 0, bend = 0, op = 0, win_lo = 0, blk_op = 0, bmax = 0, fflags = 0;  // fflags: 1 indep, 2 bsum, 4 csum
     uint32_t p_lit = 0, p_lsrc = 0, p_mlen = 0, p_off = 0;
     int err = 0;
-    uintptr_t wbase = 0;        // stream address staged at ws.win[0] (0: none)
     bool force_serial = false;  // the last speculative round made no progress: one serial round first
     uint32_t seglim = 32;       // segments per speculative round (fewer where sequences are dense: the record pool is finite)
 
@@ -431,11 +457,9 @@ __global__ void __launch_bounds__(32) lz4_decode_kernel(const uint8_t* __restric
             const uint32_t nseg = min(seglim, (bend - ip + kSeg - 1) / kSeg);  // the last segment may be short
             const uint32_t spanend = min(ip + nseg * kSeg, bend);
             const uintptr_t a0 = reinterpret_cast<uintptr_t>(src) + ip;
-            if (wbase != (a0 & ~(uintptr_t)15)) {
-                cp_async_wait_all();  // a request for another position may still be in flight
-                wbase = a0 & ~(uintptr_t)15;
-                stage_window(ws, wbase, comp_hi, lane);
-            }
+            const uintptr_t wbase = a0 & ~(uintptr_t)15;
+            __syncwarp();  // the previous round's stream-order list lives in the window
+            stage_window(ws, wbase, comp_hi, lane);
             const uint32_t wofs = (uint32_t)(a0 - wbase) - ip;
             cp_async_wait_all();
             __syncwarp();
@@ -463,7 +487,7 @@ __global__ void __launch_bounds__(32) lz4_decode_kernel(const uint8_t* __restric
                     if (slot < kPool) {
                         ws.pool[slot] = make_uint2((pos - ip) | (h.lit << 16), h.ml | (h.off << 16));
                         ws.meta[slot] = (uint16_t)((lane << 8) | cnt);
-                        idx8[pos - ip] = (uint8_t)(cnt + 1);
+                        atomicOr(&ws.bmp[(pos - ip) >> 5], 1u << ((pos - ip) & 31));
                         cnt++;
                         pos = h.nip;
                     } else
@@ -480,8 +504,19 @@ __global__ void __launch_bounds__(32) lz4_decode_kernel(const uint8_t* __restric
                 Hop h;
                 h.ok = false;
                 if (seek) {
-                    const uint32_t j = idx8[pos - ip];
-                    if (j) { nxt = (pos - ip) / kSeg; nj = j - 1; seek = false; }
+                    const uint32_t b = pos - ip;
+                    if ((ws.bmp[b >> 5] >> (b & 31)) & 1u) {
+                        // joined: the record there is number (visited positions of that segment below b) of its lane
+                        nxt = b / kSeg;
+                        nj = 0;
+                        for (uint32_t w = (nxt * kSeg) >> 5; w <= (b >> 5); w++) {
+                            uint32_t bits = ws.bmp[w];
+                            if (w == (nxt * kSeg) >> 5) bits &= ~0u << ((nxt * kSeg) & 31);
+                            if (w == (b >> 5)) bits &= (1u << (b & 31)) - 1u;
+                            nj += __popc(bits);
+                        }
+                        seek = false;
+                    }
                     else if (e == kJoinHops || used >= kPool) seek = false;  // the round ends at pos
                     else {
                         h = spec_hop(src, win, wofs, pos, bend);
@@ -532,50 +567,54 @@ __global__ void __launch_bounds__(32) lz4_decode_kernel(const uint8_t* __restric
             for (uint32_t sl = lane; sl < nrec; sl += 32) {
                 const uint32_t mt = ws.meta[sl], k = mt >> 8, q = mt & 255u;
                 const int32_t b = ws.base[k];
-                if (b != kNotTrue && q >= ws.first[k]) ws.ref[b + (int32_t)q] = (uint16_t)sl;
+                if (b != kNotTrue && q >= ws.first[k]) ref[b + (int32_t)q] = (uint16_t)sl;
             }
             const uint32_t next_ip = __shfl_sync(kFull, pos, 31 - __clz(truemask));
             __syncwarp();
-            // the window and the position map are dead from here: request the next round's now
             const bool stopped = !__shfl_sync(kFull, run, 31 - __clz(truemask));  // the true chain met something unusual
-            if (T != 0 && !stopped && bend - next_ip >= kSpecMin) {
-                wbase = (reinterpret_cast<uintptr_t>(src) + next_ip) & ~(uintptr_t)15;
-                stage_window(ws, wbase, comp_hi, lane);
-            }
             ZG_T(t_res);
 
-            // ---- execute: 32 consecutive true sequences per step
+            // ---- execute: kNP x 32 consecutive true sequences per step
             const uint32_t ip0 = ip;
             uint32_t gop = op;
             bool bad = false;
 #pragma unroll 1
-            for (uint32_t g0 = 0; g0 < T && !bad; g0 += 32) {
-                const uint32_t r = g0 + lane;
-                uint32_t prel = 0, lit = 0, ml = 0, off = 0;
-                if (r < T) {
-                    const uint2 rec = ws.pool[ws.ref[r]];
-                    prel = rec.x & 0xffffu; lit = rec.x >> 16; ml = rec.y & 0xffffu; off = rec.y >> 16;
+            for (uint32_t g0 = 0; g0 < T && !bad; g0 += 32 * kNP) {
+                uint32_t prel[kNP], lit[kNP], ml[kNP], off[kNP], dst[kNP], lit_src[kNP];
+                const uint32_t step0 = gop;
+#pragma unroll
+                for (int q = 0; q < kNP; q++) {
+                    const uint32_t r = g0 + 32 * q + lane;
+                    prel[q] = lit[q] = ml[q] = off[q] = 0;
+                    if (r < T) {
+                        const uint2 rec = ws.pool[ref[r]];
+                        prel[q] = rec.x & 0xffffu; lit[q] = rec.x >> 16; ml[q] = rec.y & 0xffffu; off[q] = rec.y >> 16;
+                    }
                 }
-                const uint32_t len = lit + ml;
-                const uint32_t sc = warp_incl_scan(len, lane);
-                const uint32_t dst = gop + sc - len;
-                // the oracle's checks that need output positions; a failing sequence goes to the serial walker
-                const bool anomaly = r < T && (off > dst + lit - win_lo || dst + len > ulen);
-                const uint32_t am = __ballot_sync(kFull, anomaly);
-                uint32_t adv = __shfl_sync(kFull, sc, 31);
-                if (am) {
-                    const int fa = __ffs(am) - 1;
-                    bad = true;
-                    ip = ip0 + __shfl_sync(kFull, prel, fa);  // resume in front of that sequence
-                    adv = __shfl_sync(kFull, dst, fa) - gop;
-                    if ((int)lane >= fa) lit = ml = 0;
+#pragma unroll
+                for (int q = 0; q < kNP; q++) {
+                    const uint32_t len = lit[q] + ml[q];
+                    const uint32_t sc = warp_incl_scan(len, lane);
+                    dst[q] = gop + sc - len;
+                    // the oracle's checks that need output positions; a failing sequence goes to the serial walker
+                    const bool anomaly = !bad && len != 0 && (off[q] > dst[q] + lit[q] - win_lo || dst[q] + len > ulen);
+                    const uint32_t am = __ballot_sync(kFull, anomaly);
+                    uint32_t adv = __shfl_sync(kFull, sc, 31);
+                    if (bad) { lit[q] = ml[q] = 0; adv = 0; }
+                    else if (am) {
+                        const int fa = __ffs(am) - 1;
+                        bad = true;
+                        ip = ip0 + __shfl_sync(kFull, prel[q], fa);  // resume in front of that sequence
+                        adv = __shfl_sync(kFull, dst[q], fa) - gop;
+                        if ((int)lane >= fa) lit[q] = ml[q] = 0;
+                    }
+                    gop += adv;
+                    // literals follow the token and the length-extension bytes (one per 255, plus the closing one)
+                    lit_src[q] = ip0 + prel[q] + 1 + (lit[q] >= 15u ? (lit[q] - 15u) / 255u + 1u : 0u);
                 }
-                // literals follow the token and the length-extension bytes (one per 255, plus the closing one)
-                const uint32_t lit_src = ip0 + prel + 1 + (lit >= 15u ? (lit - 15u) / 255u + 1u : 0u);
-                exec_group(src, lz, gop, lit_src, lit, ml, off, dst, lane);
-                gop += adv;
+                exec_group<kNP>(src, lz, step0, lit_src, lit, ml, off, dst, lane);
 #ifdef ZG_LZ4_PROFILE
-                n_true += __popc(__ballot_sync(kFull, (lit | ml) != 0));
+                for (int q = 0; q < kNP; q++) n_true += __popc(__ballot_sync(kFull, (lit[q] | ml[q]) != 0));
 #endif
             }
             op = gop;
@@ -746,7 +785,9 @@ __global__ void __launch_bounds__(32) lz4_decode_kernel(const uint8_t* __restric
             if (cnt) {  // uniform
                 const uint32_t len = lit + ml;
                 const uint32_t sc = warp_incl_scan(len, lane);
-                exec_group(src, lz, op_start, lit_src, lit, ml, off, op_start + sc - len, lane);
+                const uint32_t a_src[1] = {lit_src}, a_lit[1] = {lit}, a_off[1] = {off}, a_dst[1] = {op_start + sc - len};
+                uint32_t a_ml[1] = {ml};
+                exec_group<1>(src, lz, op_start, a_src, a_lit, a_ml, a_off, a_dst, lane);
                 __syncwarp();  // srec is rewritten next round
             }
         }
@@ -799,8 +840,8 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     cudaError_t e = cudaMemsetAsync(ticket, 0, 256, st);
     if (e != cudaSuccess) return e;
     // One warp per CTA, one chunk per warp at a time; the grid is what the machine keeps resident (shared memory
-    // allows 15 CTAs per SM) and the ticket counter feeds it, longest chunks first.  ZEST_LZ4_WARPS overrides.
-    size_t warps = 148 * 15;
+    // allows 20 CTAs per SM) and the ticket counter feeds it, longest chunks first.  ZEST_LZ4_WARPS overrides.
+    size_t warps = 148 * 20;
     if (const char* v = getenv("ZEST_LZ4_WARPS")) { long w = atol(v); if (w > 0) warps = (size_t)w; }
     if (warps > n) warps = n;
     const uint8_t* comp_hi = comp + align_up((size_t)comp_bytes, 16);
