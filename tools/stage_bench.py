@@ -122,7 +122,12 @@ def main():
             ok = check_all()
             ms = timed(k_decode, args.steps)
             if os.environ.get("ZG_PROF"):
+                g8 = (C.c_ulonglong * 8)()
+                C.CDLL(_native.LIB_PATH).zg_lz4_profile_read(g8, 1)
                 k_decode(); torch.cuda.synchronize()
+                C.CDLL(_native.LIB_PATH).zg_lz4_profile_read(g8, 0)
+                g = list(g8)
+                print(f"      execute steps {g[3]}: cycles/step pass1 {g[0]/max(g[3],1):.0f} long copies {g[1]/max(g[3],1):.0f} match rounds {g[2]/max(g[3],1):.0f}; rounds/step {g[4]/max(g[3],1):.2f} pending/round {g[5]/max(g[4],1):.1f} long lits/step {g[6]/max(g[3],1):.2f} long old matches/step {g[7]/max(g[3],1):.2f}")
                 pr = s_dec[16:88].cpu().numpy().view(np.uint64)
                 tot = float(pr[:4].sum()) or 1.0
                 print(f"      phase cycles: parse {pr[0]/tot:.3f} resolve {pr[1]/tot:.3f} execute {pr[2]/tot:.3f} serial {pr[3]/tot:.3f}  spec rounds {pr[4]} serial rounds {pr[5]}  true records {pr[6]} parsed records {pr[7]} pending matches {pr[8]}  total warp-cycles {tot:.3e}")

@@ -385,6 +385,8 @@ namespace {
 
 // One sub-batch of xorbs in flight on a lane.
 struct VerifySlot {
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // ZEST_VERIFY_TRACE: copy start / copy end / kernels end / results on host
+    double t_plan = 0, t_enq = 0;
     Lane* L = nullptr;
     bool launched = false;
     size_t x0 = 0, nx = 0;
@@ -426,11 +428,24 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
     }
     size_t hashes_written = 0;
     uint64_t verified = 0;
+    // ZEST_VERIFY_TRACE=1 (developer aid): per sub-batch, when its copies, kernels and result download started and ended
+    static const bool trace = getenv("ZEST_VERIFY_TRACE") != nullptr;
+    cudaEvent_t ev0 = nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto now_ms = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count(); };
+    if (trace) { cudaEventCreate(&ev0); cudaEventRecord(ev0, slots[0].L->st); }
 
     auto collect = [&](VerifySlot& S) -> int {  // wait for the slot's sub-batch and hand its results to the caller
         if (!S.launched) return ZG_OK;
         S.launched = false;
         CU(cudaStreamSynchronize(S.L->st));
+        if (trace && S.ev[0]) {
+            float a = 0, b = 0, c = 0, d = 0;
+            cudaEventElapsedTime(&a, ev0, S.ev[0]); cudaEventElapsedTime(&b, ev0, S.ev[1]);
+            cudaEventElapsedTime(&c, ev0, S.ev[2]); cudaEventElapsedTime(&d, ev0, S.ev[3]);
+            fprintf(stderr, "[zest trace] xorbs %zu..%zu: planned %.2f enqueued %.2f | copy %.2f-%.2f kernels -%.2f results %.2f | collected %.2f ms\n",
+                    S.x0, S.x0 + S.nx, S.t_plan, S.t_enq, a, b, c, d, now_ms());
+        }
         const uint8_t* hr = static_cast<const uint8_t*>(S.L->hres.p);
         memcpy(roots + 32 * S.x0, hr, 32 * S.nx);
         memcpy(verdict + S.x0, hr + align_up(32 * S.nx, 256), S.nx);
@@ -448,6 +463,12 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
     size_t x = 0;
     int si = 0;
     std::vector<HostIndex> ixs;
+    // Sub-batches taper: each takes at most a third of the compressed bytes still to come.  The call ends one
+    // sub-batch's kernels after the last byte has crossed the link, and a chunk is a serial chain of 1-2 ms, so the
+    // last sub-batches are kept small (they decode at single-chunk latency on a nearly empty GPU) while the early,
+    // large ones keep the machine full.
+    uint64_t comp_left = 0;
+    for (size_t i = 0; i < n; i++) comp_left += lens[i];
     while (x < n) {
         // ---- plan the next sub-batch on the host (the previous ones are running)
         ixs.clear();
@@ -455,7 +476,8 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         std::vector<uint64_t> utot;
         size_t x0 = x, nc = 0;
         uint64_t ub = 0, cb = 0;
-        while (x < n && (x == x0 || ub < sub_batch_bytes())) {
+        const uint64_t comp_cap = comp_left / 3;
+        while (x < n && (x == x0 || (ub < sub_batch_bytes() && cb < comp_cap))) {
             ixs.emplace_back();
             uint32_t c = 0;
             int wr = (!blobs[x] && lens[x]) ? ZG_ERR_INVALID_ARG : walk(blobs[x], lens[x], 0xffffffffu, &ixs.back(), &c);
@@ -463,12 +485,19 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
             else { ub += ixs.back().total_ulen + 16ull * c; cb += align_up(lens[x], 16); nc += c; }
             walk_err.push_back(wr);
             utot.push_back(ixs.back().total_ulen);
+            comp_left -= lens[x];
             x++;
         }
         size_t nx = x - x0;
         VerifySlot& S = slots[si];
+        const double t_planned = now_ms();
         if ((rc = collect(S))) break;
         Lane& L = *S.L;
+        S.t_plan = t_planned;
+        if (trace) {
+            for (auto& e : S.ev) if (!e) cudaEventCreate(&e);
+            cudaEventRecord(S.ev[0], L.st);
+        }
         S.x0 = x0; S.nx = nx; S.walk_err = walk_err; S.ulen_total = utot;
         if (chunk_hashes && hashes_written + nc > chunk_hash_cap) {
             rc = fail(ZG_ERR_CAPACITY, "chunk_hashes holds %zu hashes, the batch has more", chunk_hash_cap);
@@ -517,6 +546,7 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         uint8_t* dres = static_cast<uint8_t*>(L.res.p);
         uint8_t* scr = static_cast<uint8_t*>(L.scratch.p);
         if (e == cudaSuccess) e = cudaMemcpyAsync(dm, hm, up_bytes, cudaMemcpyHostToDevice, L.st);
+        if (trace) cudaEventRecord(S.ev[1], L.st);
         if (e == cudaSuccess)
             e = launch_decode(static_cast<const uint8_t*>(L.comp.p), cpos, reinterpret_cast<ChunkDesc*>(dm), nc, static_cast<uint8_t*>(L.out.p),
                               ub, reinterpret_cast<int32_t*>(dm + o_status), scr, sz_dec, L.st);
@@ -528,9 +558,11 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
             e = launch_merkle(dres + r_hashes, reinterpret_cast<uint32_t*>(dm + o_len), nullptr, reinterpret_cast<uint32_t*>(dm + o_first), nx,
                               nc, reinterpret_cast<int32_t*>(dm + o_status), expected ? dm + o_exp : nullptr, dres,
                               reinterpret_cast<int8_t*>(dres + r_verdict), scr + sz_dec + sz_hash, sz_mer, L.st);
+        if (trace) cudaEventRecord(S.ev[2], L.st);
         if (e == cudaSuccess) e = cudaMemcpyAsync(L.hres.p, dres, r_hashes, cudaMemcpyDeviceToHost, L.st);
         if (e == cudaSuccess && chunk_hashes && nc)
             e = cudaMemcpyAsync(chunk_hashes + 32 * hashes_written, dres + r_hashes, 32 * nc, cudaMemcpyDeviceToHost, L.st);
+        if (trace) { cudaEventRecord(S.ev[3], L.st); S.t_enq = now_ms(); }
         S.launched = true;  // even on a launch error the stream may hold work: collect() drains it
         if (e != cudaSuccess) { rc = cuda_fail(e, "verify pipeline"); break; }
         hashes_written += nc;
@@ -544,6 +576,12 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
     for (int s = 0; s < n_slots; s++) {
         int cr = collect(slots[(si + s) % n_slots]);
         if (cr && rc == ZG_OK) rc = cr;
+    }
+    if (trace) {
+        for (int s = 0; s < n_slots; s++)
+            for (auto& e : slots[s].ev) if (e) cudaEventDestroy(e);
+        cudaEventDestroy(ev0);
+        fprintf(stderr, "[zest trace] call done %.2f ms\n", now_ms());
     }
     if (bytes_verified) *bytes_verified = verified;
     return rc;

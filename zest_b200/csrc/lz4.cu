@@ -103,24 +103,41 @@ __device__ __forceinline__ uint64_t load_window(const uint8_t* p) {
 
 // Up to 16 bytes from any alignment into four words: all loads are issued before anything is stored, so a lane
 // pays one memory latency per copy instead of one per byte.  Only aligned words holding wanted bytes are read.
+// Written as predicated PTX with the address formed once: left to itself the compiler re-derives the 64-bit
+// address under every byte's predicate (~7 instructions per byte stored).
+template <bool READ_ONLY, int K>
+__device__ __forceinline__ uint32_t ld_word_if(unsigned long long w, uint32_t span) {  // word K of the run, if it holds wanted bytes
+    uint32_t v;
+    if (READ_ONLY)
+        asm volatile("{ .reg .pred p; setp.gt.u32 p, %1, %2; mov.u32 %0, 0; @p ld.global.nc.u32 %0, [%3+%2]; }"
+                     : "=r"(v) : "r"(span), "n"(4 * K), "l"(w) : "memory");
+    else
+        asm volatile("{ .reg .pred p; setp.gt.u32 p, %1, %2; mov.u32 %0, 0; @p ld.global.u32 %0, [%3+%2]; }"
+                     : "=r"(v) : "r"(span), "n"(4 * K), "l"(w) : "memory");
+    return v;
+}
 template <bool READ_ONLY>
 __device__ __forceinline__ void load16(const uint8_t* s, uint32_t n, uint32_t (&x)[4]) {
-    uintptr_t a = reinterpret_cast<uintptr_t>(s);
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-    uint32_t sh = (uint32_t)(a & 3) * 8, span = n ? (uint32_t)(a & 3) + n : 0;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(s);
+    const unsigned long long w = __cvta_generic_to_global(reinterpret_cast<const void*>(a & ~(uintptr_t)3));
+    const uint32_t sh = (uint32_t)(a & 3) * 8, span = n ? (uint32_t)(a & 3) + n : 0;
     uint32_t v[5];
-#pragma unroll
-    for (int k = 0; k < 5; k++) {
-        v[k] = 0;
-        if (span > 4u * k) v[k] = READ_ONLY ? __ldg(w + k) : w[k];
-    }
+    v[0] = ld_word_if<READ_ONLY, 0>(w, span); v[1] = ld_word_if<READ_ONLY, 1>(w, span); v[2] = ld_word_if<READ_ONLY, 2>(w, span);
+    v[3] = ld_word_if<READ_ONLY, 3>(w, span); v[4] = ld_word_if<READ_ONLY, 4>(w, span);
 #pragma unroll
     for (int k = 0; k < 4; k++) x[k] = __funnelshift_r(v[k], v[k + 1], sh);
 }
+template <int I>
+__device__ __forceinline__ void st_byte_if(unsigned long long g, uint32_t n, uint32_t word) {  // byte I of the run, if I < n
+    asm volatile("{ .reg .pred p; setp.gt.u32 p, %0, %1; @p st.global.u8 [%2+%1], %3; }"
+                 :: "r"(n), "n"(I), "l"(g), "r"(word >> (8 * (I & 3))) : "memory");
+}
 __device__ __forceinline__ void store16(uint8_t* d, uint32_t n, const uint32_t (&x)[4]) {
-#pragma unroll
-    for (int i = 0; i < 16; i++)
-        if ((uint32_t)i < n) d[i] = (uint8_t)(x[i >> 2] >> (8 * (i & 3)));
+    const unsigned long long g = __cvta_generic_to_global(d);
+    st_byte_if<0>(g, n, x[0]); st_byte_if<1>(g, n, x[0]); st_byte_if<2>(g, n, x[0]); st_byte_if<3>(g, n, x[0]);
+    st_byte_if<4>(g, n, x[1]); st_byte_if<5>(g, n, x[1]); st_byte_if<6>(g, n, x[1]); st_byte_if<7>(g, n, x[1]);
+    st_byte_if<8>(g, n, x[2]); st_byte_if<9>(g, n, x[2]); st_byte_if<10>(g, n, x[2]); st_byte_if<11>(g, n, x[2]);
+    st_byte_if<12>(g, n, x[3]); st_byte_if<13>(g, n, x[3]); st_byte_if<14>(g, n, x[3]); st_byte_if<15>(g, n, x[3]);
 }
 
 // Whole-warp copy of non-overlapping ranges, any alignment.  Destination words are written aligned; the source
@@ -505,16 +522,8 @@ __global__ void __launch_bounds__(32, 20) lz4_decode_kernel(const uint8_t* __res
                 h.ok = false;
                 if (seek) {
                     const uint32_t b = pos - ip;
-                    if ((ws.bmp[b >> 5] >> (b & 31)) & 1u) {
-                        // joined: the record there is number (visited positions of that segment below b) of its lane
+                    if ((ws.bmp[b >> 5] >> (b & 31)) & 1u) {  // joined
                         nxt = b / kSeg;
-                        nj = 0;
-                        for (uint32_t w = (nxt * kSeg) >> 5; w <= (b >> 5); w++) {
-                            uint32_t bits = ws.bmp[w];
-                            if (w == (nxt * kSeg) >> 5) bits &= ~0u << ((nxt * kSeg) & 31);
-                            if (w == (b >> 5)) bits &= (1u << (b & 31)) - 1u;
-                            nj += __popc(bits);
-                        }
                         seek = false;
                     }
                     else if (e == kJoinHops || used >= kPool) seek = false;  // the round ends at pos
@@ -535,6 +544,18 @@ __global__ void __launch_bounds__(32, 20) lz4_decode_kernel(const uint8_t* __res
                         if (pos >= spanend) seek = false;
                     } else
                         seek = false;
+                }
+            }
+            if (nxt < 32) {
+                // the record joined is number (visited positions of its segment below the join) of its lane
+                const uint32_t lo = nxt * kSeg, hi = pos - ip;  // bits [lo, hi) of the map; hi - lo < kSeg
+#pragma unroll
+                for (uint32_t w = 0; w < 4; w++) {
+                    const uint32_t wi = (lo >> 5) + w, b0 = wi << 5;
+                    uint32_t bits = (wi < kSpanMax / 32 && b0 < hi) ? ws.bmp[wi] : 0u;
+                    if (b0 < lo) bits &= ~0u << (lo - b0);
+                    if (hi - b0 < 32u) bits &= (1u << (hi - b0)) - 1u;
+                    nj += __popc(bits);
                 }
             }
             // the next round takes fewer segments when this one ran out of record slots, more when it used few
