@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Developer tool: time the decode / hash / merkle / cdc kernels alone on one workload, optionally sweeping the
-decode kernel's tuning knobs.  Not part of the product or of bench.py's contract.
-  python tools/stage_bench.py --workload gpt2-lz4 --bytes 550000000 --sweep "1,2,4,8,16,32"
+decode kernel's grid size (ZEST_LZ4_WARPS).  Not part of the product or of bench.py's contract.
+  python tools/stage_bench.py --workload gpt2-lz4 --bytes 550000000 --warps 1480,2220,2960
+With a library built with -DZG_LZ4_PROFILE, ZG_PROF=1 prints the decoder's phase counters.
 """
 import argparse
 import ctypes as C
@@ -26,9 +27,7 @@ def main():
     ap.add_argument("--workload", default="gpt2-lz4")
     ap.add_argument("--bytes", type=int, default=0)
     ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--sweep", default="")
     ap.add_argument("--warps", default="")
-    ap.add_argument("--oversub", default="")
     ap.add_argument("--cdc", action="store_true")
     args = ap.parse_args()
     nbytes = args.bytes or bench.WORKLOADS[args.workload]["nbytes"]
@@ -105,17 +104,13 @@ def main():
         return ok
 
     res = {}
-    sweeps = [s for s in args.sweep.split(",") if s] or [""]
+    sweeps = [""]
     warps = [w for w in args.warps.split(",") if w] or [""]
-    overs = [o for o in args.oversub.split(",") if o] or [""]
+    overs = [""]
     for w in [(a, b) for a in warps for b in overs]:
         w, ov = w
-        if ov:
-            os.environ["ZEST_LZ4_OVERSUB"] = ov
         for s in sweeps:
-            os.environ.pop("ZEST_LZ4_SLOTS", None); os.environ.pop("ZEST_LZ4_WARPS", None)
-            if s:
-                os.environ["ZEST_LZ4_SLOTS"] = s
+            os.environ.pop("ZEST_LZ4_WARPS", None)
             if w:
                 os.environ["ZEST_LZ4_WARPS"] = w
             d_out.zero_()
@@ -131,9 +126,9 @@ def main():
                 pr = s_dec[16:88].cpu().numpy().view(np.uint64)
                 tot = float(pr[:4].sum()) or 1.0
                 print(f"      phase cycles: parse {pr[0]/tot:.3f} resolve {pr[1]/tot:.3f} execute {pr[2]/tot:.3f} serial {pr[3]/tot:.3f}  spec rounds {pr[4]} serial rounds {pr[5]}  true records {pr[6]} parsed records {pr[7]} pending matches {pr[8]}  total warp-cycles {tot:.3e}")
-            print(f"decode slots={s or 'auto':>4} warps={w or 'auto':>5} oversub={ov or 'auto':>2}: {ms:8.3f} ms  {total/ms/1e6:8.1f} GB/s uncompressed  {(total+comp_bytes)/ms/1e6:8.1f} GB/s alg  parity={'ok' if ok else 'FAIL'}", flush=True)
+            print(f"decode warps={w or 'auto':>5}: {ms:8.3f} ms  {total/ms/1e6:8.1f} GB/s uncompressed  {(total+comp_bytes)/ms/1e6:8.1f} GB/s alg  parity={'ok' if ok else 'FAIL'}", flush=True)
             res[f"decode_s{s}_w{w}"] = ms
-    os.environ.pop("ZEST_LZ4_SLOTS", None); os.environ.pop("ZEST_LZ4_WARPS", None)
+    os.environ.pop("ZEST_LZ4_WARPS", None)
     ms = timed(k_hash, args.steps)
     print(f"hash   : {ms:8.3f} ms  {total/ms/1e6:8.1f} GB/s")
     ms = timed(k_merkle, args.steps)

@@ -6,32 +6,36 @@
 // lz4_block, oz_decode_chunk), whose checks are mirrored one for one and in the same order so that a malformed
 // chunk gets the same error code on both sides.
 //
-// Mapping.  One warp decodes one chunk at a time (chunks are handed out longest-first through a ticket counter).
-// LZ4's token stream is serial, and on real Xet data the sequences are tiny (text: ~5,900 per 64 KiB chunk, ~11
-// output bytes each), so a lane-serial walk leaves 31 lanes idle and costs ~100 warp instructions per sequence.
-// The walk is therefore SPECULATIVE and warp-wide:
-//   parse   : the next 32 x 68 stream bytes of the block are staged in shared memory and cut into 32 segments;
-//             lane k walks tokens from the first byte of segment k as if a sequence started there.  Lane 0 starts
-//             at the true position.  A chain that starts on a wrong byte falls onto true sequence boundaries
-//             after a few hops (every hop lands on a boundary with probability ~1/sequence length, and once on
-//             one it stays on them), so each lane also walks a few hops into its neighbour's segment until it
-//             reaches a position its neighbour visited -- the JOIN.  Positions visited are kept in a byte map.
-//   resolve : lane 0 is true; a lane is true from its join index on iff the chain before it is true and joined
+// Mapping.  One warp decodes one chunk at a time (chunks are handed out longest-first through a ticket counter,
+// 20 single-warp CTAs per SM).  LZ4's token stream is serial, and on real Xet data the sequences are tiny (text:
+// ~5,900 per 64 KiB chunk, ~11 output bytes each), so a lane-serial walk leaves 31 lanes idle and costs ~100 warp
+// instructions per sequence.  The walk is therefore SPECULATIVE and warp-wide, in rounds:
+//   parse   : the next 32 x 68 stream bytes of the block are staged in shared memory (cp.async) and cut into 32
+//             segments; lane k walks tokens from the first byte of segment k as if a sequence started there.  Lane 0
+//             starts at the true position.  A chain that starts on a wrong byte falls onto true sequence boundaries
+//             after a few hops (each hop lands on one with probability ~1/sequence length, and once on one it stays
+//             on them; measured on text: median 29 bytes, 95 % within 155), so after its own segment every lane
+//             walks on into the following ones until it reaches a position that segment's own chain visited -- the
+//             JOIN.  Visited positions are one bit each in a shared bit map; records (position, literal length,
+//             match length, offset; 8 bytes) go to a pool whose slots are handed out per iteration by ballot.
+//   resolve : lane 0 is true; a lane is true from its join position on iff the chain before it is true and joined
 //             it (pointer doubling over the join links, 5 shuffle rounds).  True records are numbered in stream
-//             order by a warp scan.  A chain that meets anything unusual (block end near, oversized length, zero
-//             offset) simply stops; if it was the true chain, the serial walker takes over from that byte.
+//             order by a warp scan.  A chain that meets anything unusual (end of block, oversized length, zero
+//             offset, pool full) simply stops; if it was the true chain, the serial walker takes over at that byte.
 //   execute : 32 consecutive true sequences per step, one per lane: output positions by a warp scan of the lengths,
 //             the offset/size checks of the oracle on those positions, then literals and matches whose source
-//             precedes the step in one pass, and the few matches that read the step's own output in frontier
-//             rounds.  Long runs (incompressible planes, zero runs) are copied by the whole warp.
-//   serial  : frame and block headers, the last bytes of a block, stored blocks, oversized pieces and every error
+//             precedes the step in one pass (all loads before all stores), and the matches that read the step's
+//             own output in frontier rounds.  Runs longer than 16 bytes are copied by the whole warp.
+//   serial  : frame and block headers, the last sequence of a block, stored blocks, oversized pieces and every error
 //             go through a plain one-sequence-at-a-time walker that mirrors the oracle check for check; it runs
 //             uniformly on all lanes (same instructions, no broadcasts) and feeds the same execute step.
 // Output goes to global memory (a 64 MiB xorb stays resident in the 126 MB L2); byte-group regrouping is done by
 // the warp when a scheme-2 chunk completes, reading the planes back from L2.
 //
-// Roofline: HBM-bound in principle (compressed bytes in + decoded bytes out); in practice bounded by issue slots
-// and dependent-instruction latency per sequence.  bench.py reports achieved GB/s over those algorithmic bytes.
+// Roofline: HBM-bound in principle (compressed bytes in + decoded bytes out).  In practice the kernel is bound by
+// instruction issue: ~36 warp instructions per sequence (profiles/r1_ncu_decode_spec*.txt), 55 % of the issue
+// slots busy with 20 warps per SM, the rest lost to dependent-instruction and memory latency inside each chunk's
+// chain.  bench.py reports achieved GB/s over the algorithmic bytes.
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -56,7 +60,10 @@ constexpr uint32_t kSerialCap = 16;   // sequences per round of the serial walke
 constexpr uint32_t kSeg = 68;         // speculative segment, stream bytes: 17 words, so 32 lanes start in 32 banks
 constexpr uint32_t kCap = 24;         // a 68-byte segment holds at most 23 sequences
 constexpr uint32_t kJoinHops = 64;    // sequences a chain may walk beyond its segment looking for its join
-constexpr uint32_t kPool = 704;       // records per round, all lanes together (slots are handed out per iteration)
+#ifndef ZG_POOL
+#define ZG_POOL 704
+#endif
+constexpr uint32_t kPool = ZG_POOL;       // records per round, all lanes together (slots are handed out per iteration)
 constexpr uint32_t kSpanMax = 32 * kSeg;
 constexpr uint32_t kWinBytes = 2304;  // staged stream bytes: alignment slack + span + >= 100 bytes beyond it
 constexpr int32_t kNotTrue = INT32_MIN;
@@ -419,7 +426,10 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
     return v;
 }
 
-__global__ void __launch_bounds__(32, 20) lz4_decode_kernel(const uint8_t* __restrict__ comp, const ChunkDesc* __restrict__ chunks,
+#ifndef ZG_MIN_CTAS
+#define ZG_MIN_CTAS 20
+#endif
+__global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8_t* __restrict__ comp, const ChunkDesc* __restrict__ chunks,
                                                         uint32_t n_chunks, uint8_t* out, uint8_t* tmp,
                                                         int32_t* __restrict__ status, uint32_t* ticket, const uint8_t* comp_hi) {
     __shared__ __align__(16) WarpShared ws;
@@ -862,7 +872,19 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     if (e != cudaSuccess) return e;
     // One warp per CTA, one chunk per warp at a time; the grid is what the machine keeps resident (shared memory
     // allows 20 CTAs per SM) and the ticket counter feeds it, longest chunks first.  ZEST_LZ4_WARPS overrides.
-    size_t warps = 148 * 20;
+    static int ctas_per_sm = 0, sms = 0;  // same answer from every thread that gets here first
+    if (ctas_per_sm == 0) {
+        int dev = 0, occ = 0, n_sm = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lz4_decode_kernel, 32, 0) == cudaSuccess && occ > 0 && n_sm > 0) {
+            sms = n_sm;
+            ctas_per_sm = occ;
+        } else {
+            sms = 148;
+            ctas_per_sm = 20;
+        }
+    }
+    size_t warps = (size_t)sms * ctas_per_sm;
     if (const char* v = getenv("ZEST_LZ4_WARPS")) { long w = atol(v); if (w > 0) warps = (size_t)w; }
     if (warps > n) warps = n;
     const uint8_t* comp_hi = comp + align_up((size_t)comp_bytes, 16);
