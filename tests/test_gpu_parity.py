@@ -240,6 +240,59 @@ def test_corruption_verdicts_match_oracle(ctx, oracle, vectors):
     assert (got.verdict <= 0).sum() >= len(blobs) - 3 - 6   # nearly every flip is caught (a flip in padding may not be)
 
 
+def test_decode_chunk_size_sweep(ctx, oracle):
+    """Chunks of every size from 1 to 700 bytes and a run of sizes around the decoder's round geometry (its
+    speculative walk cuts a block into 68-byte segments, 32 per round): each must decode bit-exact under both
+    compression schemes, whatever the block length is modulo the segment and the span."""
+    text = oracle.synth_zipf_text(3_000_000, 11)
+    bf = oracle.synth_bf16(3_000_000, 12)
+    sizes = list(range(1, 701)) + list(range(2100, 2400, 7)) + list(range(4200, 4500, 13)) + [8191, 8192, 8193, 40_000]
+    ends = np.cumsum(np.array(sizes, np.uint64))
+    total = int(ends[-1])
+    for data, policy in ((text, 1), (text, 2), (bf, 2), (bf, 1)):
+        d = data[:total]
+        blob = oracle.build_xorb(d, ends, policy)
+        n = len(sizes)
+        assert oracle.extract_chunk_range(blob, 0, n) == d.tobytes()
+        assert z.XorbReader(blob, ctx).extract_chunk_range(0, n) == d.tobytes()
+        off = np.concatenate([np.zeros(1, np.uint64), ends])
+        root = oracle.merkle_root(oracle.hash_chunks(d, off), np.diff(off))
+        assert z.verify_xorbs([blob], [root], ctx=ctx).ok
+
+
+def test_decode_fuzz_payload(ctx, oracle):
+    """Random damage inside the LZ4 payload of real-sized chunks (text / LZ4 and bf16 / BG4-LZ4), one damaged chunk
+    per xorb: the verdict must be the oracle's, and where the damaged stream still decodes (a flipped literal, a
+    changed length that happens to stay consistent) the root must be the oracle's too -- i.e. the decoded bytes are
+    the same even for streams no compressor would emit."""
+    rng = np.random.default_rng(4242)
+    blobs = []
+    for data, policy in ((oracle.synth_zipf_text(400_000, 21), 1), (oracle.synth_bf16(400_000, 22), 2)):
+        xs, _, _ = oracle.make_xorbs(data, policy)
+        blob = xs[0].blob
+        ix = oracle.xorb_index(blob)
+        for c in range(min(4, ix.n)):
+            lo = int(ix.hdr_off[c]); clen = int(ix.clen[c])
+            rec = blob[lo:lo + 8 + clen]
+            for _ in range(300):
+                b = bytearray(rec)
+                k = int(rng.integers(1, 5))
+                for _ in range(k):
+                    pos = int(rng.integers(8 + 11, len(b) - 4))      # past the frame header and first block size
+                    mode = int(rng.integers(0, 4))
+                    if mode == 0: b[pos] ^= 1 << int(rng.integers(0, 8))
+                    elif mode == 1: b[pos] = int(rng.integers(0, 256))
+                    elif mode == 2: b[pos] = 0xff
+                    else: b[pos] = 0
+                blobs.append(bytes(b))
+    got = z.verify_xorbs(blobs, ctx=ctx)
+    want_v, want_roots, _ = oracle.verify_xorbs(blobs, threads=8)
+    assert list(got.verdict) == list(want_v)
+    ok = want_v >= 0
+    assert ok.sum() > 100 and (~ok).sum() > 500          # both outcomes are well represented
+    assert (got.roots[ok] == want_roots[ok]).all()
+
+
 def test_many_xorbs_batch(ctx, oracle):
     """A batch that spans several sub-batches and both pipeline lanes, mixed schemes, one corrupt in the middle."""
     blobs, expected = [], []
