@@ -126,6 +126,15 @@ ZG_API int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_
 ZG_API int zg_hash_chunks(zg_ctx* ctx, const uint8_t* data, const uint64_t* offsets, size_t n, const uint8_t* key,
                    uint8_t* out_hashes);
 
+/* Verification ("range") hashes of reconstruction terms: term t covers the chunks bounds[t] .. bounds[t+1]-1 of the
+ * chunk-hash list and its hash is BLAKE3.keyed(VERIFICATION_KEY, those 32-byte hashes back to back) -- the value a
+ * Xet shard stores beside every term (xet-core mdb_shard FileVerificationEntry).  With it the bytes a term
+ * contributed in XetBridge.reconstructToFile (src/xet_bridge.zig:231-264: one extractChunkRange per term) can be
+ * checked against the file's metadata: extract, zg_hash_chunks, zg_range_hashes, compare.  zest itself does not
+ * verify terms today.  out holds n_terms x 32 bytes. */
+ZG_API int zg_range_hashes(zg_ctx* ctx, const uint8_t* chunk_hashes, const uint32_t* bounds /* n_terms + 1 chunk indices */,
+                    size_t n_terms, uint8_t* out);
+
 /* Merkle root of (hash, length) pairs -- zig-xet hashing's aggregated node hash (CONTRIBUTING.md:144-146).
  * file_hash != 0 additionally applies the zero-key file-hash step (the value hf_xet.hash_files reports). */
 ZG_API int zg_merkle_root(zg_ctx* ctx, const uint8_t* hashes, const uint64_t* lens, size_t n, int file_hash,

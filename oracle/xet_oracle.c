@@ -324,6 +324,19 @@ OZ_API void oz_file_hash(const uint8_t* hashes, const uint64_t* lens, size_t n, 
     oz_blake3_keyed(zero, root, 32, out);
 }
 
+/* Term verification ("range") hash: BLAKE3.keyed(VERIFICATION_KEY, h[s] || h[s+1] || ... || h[e-1]) over the chunk
+ * hashes of one reconstruction term.  This is xet-core's mdb_shard chunk_verification
+ * (range_hash_from_chunks); the key and the construction were confirmed here against the FileVerificationEntry
+ * rows hf_xet 1.5.0 writes into its .mdb shards (tests/golden/make_golden.py: shard_range_hashes). */
+static const uint8_t XET_VERIFICATION_KEY[32] = {127, 24,  87,  214, 206, 86,  237, 102, 18,  127, 249,
+                                                 19,  231, 165, 195, 243, 164, 205, 38,  213, 181, 219,
+                                                 73,  230, 65,  36,  152, 127, 40,  251, 148, 195};
+/* bounds[0..n_terms] are chunk indices; term t covers hashes[bounds[t] .. bounds[t+1]). */
+OZ_API void oz_range_hashes(const uint8_t* hashes, const uint32_t* bounds, size_t n_terms, uint8_t* out) {
+    for (size_t t = 0; t < n_terms; t++)
+        oz_blake3_keyed(XET_VERIFICATION_KEY, hashes + 32 * (size_t)bounds[t], 32 * (size_t)(bounds[t + 1] - bounds[t]), out + 32 * t);
+}
+
 /* ------------------------------------------------------------------------------------------------ */
 /* A.4b  LZ4 frame decode                                                                           */
 /* ------------------------------------------------------------------------------------------------ */

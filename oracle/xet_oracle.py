@@ -57,6 +57,7 @@ def lib():
         L.oz_hash_to_hex.argtypes = [u8p, C.c_char_p]
         L.oz_merkle_root.argtypes = [u8p, u64p, C.c_size_t, u8p]
         L.oz_file_hash.argtypes = [u8p, u64p, C.c_size_t, u8p]
+        L.oz_range_hashes.argtypes = [u8p, u32p, C.c_size_t, u8p]
         L.oz_xxh32.argtypes = [u8p, C.c_size_t, C.c_uint32]
         L.oz_xxh32.restype = C.c_uint32
         L.oz_xorb_index.argtypes = [u8p, C.c_size_t, C.c_size_t, u64p, u32p, u32p, u8p, u64p]
@@ -150,6 +151,16 @@ def file_hash(hashes, lens) -> bytes:
     out = np.empty(32, np.uint8)
     lib().oz_file_hash(_p(h), _p(l), l.size, _p(out))
     return out.tobytes()
+
+
+def range_hashes(hashes, bounds) -> np.ndarray:
+    """Term verification hashes: one per [bounds[t], bounds[t+1]) run of chunk hashes -> (n_terms, 32) u8."""
+    h = np.ascontiguousarray(np.asarray(hashes, np.uint8).reshape(-1, 32))
+    b = np.ascontiguousarray(np.asarray(bounds, np.uint32))
+    out = np.empty((max(b.size - 1, 0), 32), np.uint8)
+    if out.shape[0]:
+        lib().oz_range_hashes(_p(h), _p(b), out.shape[0], _p(out))
+    return out
 
 
 # ---------------------------------------------------------------- xorb stream

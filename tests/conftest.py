@@ -52,6 +52,8 @@ def golden_input(name: str) -> np.ndarray:
         b = g.integers(0, 256, 8191, dtype=np.uint8)
         c = g.integers(0, 256, 8192, dtype=np.uint8)
         return {"seed1_8MiB": a, "seed1_next_8191": b, "seed1_next_8192": c}[name]
+    if name == "seed4_70MiB":
+        return rng(4).integers(0, 256, 70 << 20, dtype=np.uint8)
     if name == "zeros_1MiB":
         return np.zeros(1 << 20, np.uint8)
     if name == "bf16_seed2_4MiB":

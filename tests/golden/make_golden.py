@@ -202,12 +202,80 @@ def real_xorbs():
     return meta
 
 
+def shard_terms(data: bytes, policy: str):
+    """Upload `data` to a local:// endpoint and read the file's reconstruction terms back from the .mdb shard
+    xet-core writes: per term the xorb hash, the chunk index range inside that xorb, the unpacked byte count and
+    the FileVerificationEntry range hash (raw byte order).  Shard layout (xet spec, "MDB shard file format"):
+    48-byte header, then per file a 48-byte header row {file hash, flags u32, n_entries u32, ..}, n_entries rows
+    {xorb hash, cas_flags u32, unpacked_bytes u32, chunk_start u32, chunk_end u32}, then -- when flags has bit 31 --
+    n_entries verification rows {range hash, 16 unused}, then -- bit 30 -- one metadata row; a row of 0xFF ends
+    the section."""
+    import glob
+    import hf_xet
+    d = tempfile.mkdtemp(prefix="xetgold")
+    os.environ["HF_XET_XORB_COMPRESSION_POLICY"] = policy
+    try:
+        s = hf_xet.XetSession()
+        with s.new_upload_commit(endpoint="local://" + d) as c:
+            h = c.start_upload_bytes(data)
+        fh = h.result().xet_info.hash
+        terms = []
+        for p in sorted(glob.glob(os.path.join(d, "xet", "xorbs", "shards", "*.mdb"))):
+            b = open(p, "rb").read()
+            pos = 48
+            while b[pos:pos + 32] != b"\xff" * 32:
+                fhash = b[pos:pos + 32]
+                flags, n = struct.unpack("<II", b[pos + 32:pos + 40])
+                pos += 48
+                rows = [b[pos + 48 * i:pos + 48 * i + 48] for i in range(n)]
+                pos += 48 * n
+                assert flags & 0x80000000, "no verification entries"
+                ver = [b[pos + 48 * i:pos + 48 * i + 32] for i in range(n)]
+                pos += 48 * n
+                if flags & 0x40000000:
+                    pos += 48
+                if to_hex(fhash) != fh:
+                    continue
+                for r, v in zip(rows, ver):
+                    _, unpacked, cs, ce = struct.unpack("<IIII", r[32:48])
+                    terms.append({"xorb_hash": to_hex(r[:32]), "chunk_start": cs, "chunk_end": ce, "unpacked": unpacked,
+                                  "range_hash": v.hex()})
+        return fh, terms
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+
+
+def term_kats():
+    """Reconstruction terms with their verification ("range") hashes, SURVEY.md 8f item 3: one-term files of 1 to
+    ~130 chunks and a 70 MiB file that spans two xorbs (two terms)."""
+    rng1 = np.random.default_rng(1)
+    cases = [
+        ("hello_world", b"hello world", "auto"),
+        ("seed0_1MiB", np.random.default_rng(0).integers(0, 256, 1 << 20, dtype=np.uint8).tobytes(), "auto"),
+        ("seed1_8MiB", rng1.integers(0, 256, 8 << 20, dtype=np.uint8).tobytes(), "auto"),
+        ("zipf_seed3_2MiB", zipf_text(2 << 20, 3), "lz4"),
+        ("seed4_70MiB", np.random.default_rng(4).integers(0, 256, 70 << 20, dtype=np.uint8).tobytes(), "auto"),
+    ]
+    out = []
+    for name, data, policy in cases:
+        fh, terms = shard_terms(data, policy)
+        assert terms and sum(t["unpacked"] for t in terms) == len(data), (name, terms)
+        print(name, fh, [(t["chunk_start"], t["chunk_end"]) for t in terms])
+        out.append({"name": name, "n_bytes": len(data), "file_hash": fh, "terms": terms})
+    return out
+
+
 def main():
-    res = {"generator": "tests/golden/make_golden.py", "hf_xet": "1.5.0", "blake3_pypi": "1.0.8",
-           "gear_table_sha256": check_gear_table(),
-           "blake3": blake3_kats(), "xet": xet_kats(), "real_xorbs": real_xorbs()}
-    json.dump(res, open(os.path.join(HERE, "vectors.json"), "w"), indent=0)
-    print("wrote", os.path.join(HERE, "vectors.json"))
+    path = os.path.join(HERE, "vectors.json")
+    if "--only-terms" in sys.argv:      # add the term vectors to an existing file without redoing the rest
+        res = json.load(open(path))
+        res["terms"] = term_kats()
+    else:
+        res = {"generator": "tests/golden/make_golden.py", "hf_xet": "1.5.0", "blake3_pypi": "1.0.8",
+               "gear_table_sha256": check_gear_table(),
+               "blake3": blake3_kats(), "xet": xet_kats(), "real_xorbs": real_xorbs(), "terms": term_kats()}
+    json.dump(res, open(path, "w"), indent=0)
+    print("wrote", path)
 
 
 if __name__ == "__main__":

@@ -340,6 +340,29 @@ def test_concurrent_callers(ctx, oracle, vectors):
     assert not errors, errors[:3]
 
 
+def test_range_hashes(ctx, oracle, vectors):
+    """zg_range_hashes against the range hashes in hf_xet's shards (golden) and, for random term partitions of a
+    long chunk-hash list (empty terms, single-chunk terms, one term of everything), against the oracle."""
+    for rec in vectors["terms"]:
+        data = golden_input(rec["name"])
+        ends, hashes, fh = z.cdc_hash(data, ctx=ctx)
+        assert z.hash_to_hex(fh) == rec["file_hash"]
+        bounds = np.concatenate([[0], np.cumsum([t["chunk_end"] - t["chunk_start"] for t in rec["terms"]])]).astype(np.uint32)
+        assert int(bounds[-1]) == ends.size
+        got = z.range_hashes(hashes, bounds, ctx=ctx)
+        assert [g.tobytes().hex() for g in got] == [t["range_hash"] for t in rec["terms"]]
+    rng = np.random.default_rng(9)
+    hashes = rng.integers(0, 256, (5000, 32), dtype=np.uint8)
+    for k in (1, 2, 7, 400, 4999):
+        cuts = np.sort(rng.integers(0, 5001, k - 1)) if k > 1 else np.zeros(0, np.int64)
+        bounds = np.concatenate([[0], cuts, [5000]]).astype(np.uint32)
+        assert (z.range_hashes(hashes, bounds, ctx=ctx) == oracle.range_hashes(hashes, bounds)).all()
+    assert z.range_hashes(hashes, [3, 3], ctx=ctx)[0].tobytes() == oracle.range_hashes(hashes, [3, 3])[0].tobytes()
+    assert z.range_hashes(hashes, [], ctx=ctx).shape == (0, 32)
+    with pytest.raises(z.ZestGpuError):
+        z.range_hashes(hashes, [5, 2], ctx=ctx)
+
+
 # ------------------------------------------------------------------------------------------------ CDC
 @pytest.mark.parametrize("name", ["seed0_1MiB", "seed1_8MiB", "zeros_1MiB", "seed1_next_8191", "seed1_next_8192",
                                   "bf16_seed2_4MiB", "zipf_seed3_2MiB", "hello_world", "empty"])

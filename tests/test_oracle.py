@@ -151,3 +151,28 @@ def test_crafted_streams(oracle):
         blk, want = craft_lz4_block(rng, n, style)
         stream = chunk_record(frame_single_block(blk, len(want)), 1, len(want))
         assert oracle.extract_chunk_range(stream, 0, 1) == want
+
+
+def test_range_hashes_against_hf_xet_shards(oracle, vectors):
+    """Term verification hashes: for every golden file the chunk hashes of each term, keyed
+    with xet-core's VERIFICATION_KEY, give the range hash hf_xet wrote into its shard -- including the two-term
+    70 MiB file, whose first xorb closes at 1,021 chunks."""
+    from conftest import golden_input
+    for rec in vectors["terms"]:
+        data = golden_input(rec["name"])
+        ends = oracle.cdc(data)
+        off = np.concatenate([np.zeros(1, np.uint64), ends])
+        hashes = oracle.hash_chunks(data, off, threads=8)
+        lens = np.diff(off)
+        assert oracle.hash_to_hex(oracle.file_hash(hashes, lens)) == rec["file_hash"]
+        base, bounds = 0, [0]
+        for t in rec["terms"]:
+            assert t["chunk_start"] == 0                      # each term starts a fresh xorb in these files
+            n = t["chunk_end"] - t["chunk_start"]
+            assert int(lens[base:base + n].sum()) == t["unpacked"]
+            assert oracle.hash_to_hex(oracle.merkle_root(hashes[base:base + n], lens[base:base + n])) == t["xorb_hash"]
+            base += n
+            bounds.append(base)
+        assert base == ends.size
+        got = oracle.range_hashes(hashes, bounds)
+        assert [g.tobytes().hex() for g in got] == [t["range_hash"] for t in rec["terms"]]

@@ -23,7 +23,7 @@ ERR_NAMES = {
 SYMBOLS = [
     "zg_init", "zg_shutdown", "zg_strerror", "zg_last_error", "zg_pinned_alloc", "zg_pinned_free", "zg_hash_to_hex",
     "zg_hex_to_hash", "zg_xorb_index", "zg_chunk_range_size", "zg_extract_chunk_range", "zg_verify_xorbs",
-    "zg_hash_chunks", "zg_merkle_root", "zg_cdc", "zg_cdc_hash", "zg_dev_hash_scratch_bytes", "zg_dev_hash_chunks",
+    "zg_hash_chunks", "zg_range_hashes", "zg_merkle_root", "zg_cdc", "zg_cdc_hash", "zg_dev_hash_scratch_bytes", "zg_dev_hash_chunks",
     "zg_dev_decode_scratch_bytes", "zg_dev_decode_chunks", "zg_dev_merkle_scratch_bytes", "zg_dev_merkle",
     "zg_dev_verify_scratch_bytes", "zg_dev_verify_xorbs", "zg_dev_cdc_scratch_bytes", "zg_dev_cdc", "zg_get_stats",
     "zg_chunk_order", "zg_dev_hash_chunks_static", "zg_xorb_footer_bytes", "zg_xorb_footer", "zg_dev_int_pipe_peak",
@@ -85,6 +85,7 @@ def lib() -> C.CDLL:
         L.zg_verify_xorbs.argtypes = [vp, vp, vp, vp, sz, vp, vp, vp, sz, C.POINTER(u64)]
         L.zg_hash_chunks.argtypes = [vp, vp, vp, sz, vp, vp]
         L.zg_merkle_root.argtypes = [vp, vp, vp, sz, i32, vp]
+        L.zg_range_hashes.argtypes = [vp, vp, vp, sz, vp]
         L.zg_cdc.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz)]
         L.zg_cdc_hash.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz), vp, vp]
         L.zg_dev_hash_scratch_bytes.argtypes = [u64, sz]

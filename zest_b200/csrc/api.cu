@@ -463,12 +463,6 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
     size_t x = 0;
     int si = 0;
     std::vector<HostIndex> ixs;
-    // Sub-batches taper: each takes at most a third of the compressed bytes still to come.  The call ends one
-    // sub-batch's kernels after the last byte has crossed the link, and a chunk is a serial chain of 1-2 ms, so the
-    // last sub-batches are kept small (they decode at single-chunk latency on a nearly empty GPU) while the early,
-    // large ones keep the machine full.
-    uint64_t comp_left = 0;
-    for (size_t i = 0; i < n; i++) comp_left += lens[i];
     while (x < n) {
         // ---- plan the next sub-batch on the host (the previous ones are running)
         ixs.clear();
@@ -476,8 +470,7 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         std::vector<uint64_t> utot;
         size_t x0 = x, nc = 0;
         uint64_t ub = 0, cb = 0;
-        const uint64_t comp_cap = comp_left / 3;
-        while (x < n && (x == x0 || (ub < sub_batch_bytes() && cb < comp_cap))) {
+        while (x < n && (x == x0 || ub < sub_batch_bytes())) {
             ixs.emplace_back();
             uint32_t c = 0;
             int wr = (!blobs[x] && lens[x]) ? ZG_ERR_INVALID_ARG : walk(blobs[x], lens[x], 0xffffffffu, &ixs.back(), &c);
@@ -485,7 +478,6 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
             else { ub += ixs.back().total_ulen + 16ull * c; cb += align_up(lens[x], 16); nc += c; }
             walk_err.push_back(wr);
             utot.push_back(ixs.back().total_ulen);
-            comp_left -= lens[x];
             x++;
         }
         size_t nx = x - x0;
@@ -618,6 +610,24 @@ int zg_hash_chunks(zg_ctx* ctx, const uint8_t* data, const uint64_t* offsets, si
     ctx->d2h += 32 * n;
     ctx->hashed += n;
     return ZG_OK;
+}
+
+// xet-core's VERIFICATION_KEY (mdb_shard chunk_verification); pinned against hf_xet shards in tests/golden/vectors.json "terms"
+static const uint8_t kVerificationKey[32] = {127, 24,  87,  214, 206, 86,  237, 102, 18,  127, 249, 19,  231, 165, 195, 243,
+                                             164, 205, 38,  213, 181, 219, 73,  230, 65,  36,  152, 127, 40,  251, 148, 195};
+
+int zg_range_hashes(zg_ctx* ctx, const uint8_t* chunk_hashes, const uint32_t* bounds, size_t n_terms, uint8_t* out) {
+    int r = check_ctx(ctx);
+    if (r) return r;
+    if (n_terms == 0) return ZG_OK;
+    if (!chunk_hashes || !bounds || !out) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    std::vector<uint64_t> off(n_terms + 1);
+    for (size_t t = 0; t <= n_terms; t++) {
+        if (t && bounds[t] < bounds[t - 1]) return fail(ZG_ERR_INVALID_ARG, "bounds must be non-decreasing (at %zu)", t);
+        off[t] = 32ull * bounds[t];
+    }
+    // one keyed BLAKE3 per term over its run of 32-byte chunk hashes: the chunk-hash kernel with another key
+    return zg_hash_chunks(ctx, chunk_hashes, off.data(), n_terms, kVerificationKey, out);
 }
 
 int zg_merkle_root(zg_ctx* ctx, const uint8_t* hashes, const uint64_t* lens, size_t n, int file_hash, uint8_t out[32]) {

@@ -78,6 +78,20 @@ def file_hash(hashes, lens, ctx: Context | None = None) -> bytes:
     return _merkle(hashes, lens, 1, ctx)
 
 
+def range_hashes(chunk_hashes, bounds, ctx: Context | None = None) -> np.ndarray:
+    """Verification hashes of reconstruction terms: term t covers chunks bounds[t] .. bounds[t+1]-1 of the list.
+    -> (n_terms, 32) u8.  Compare with the range hash a Xet shard stores beside each term."""
+    ctx = ctx or default_context()
+    h = np.ascontiguousarray(chunk_hashes, dtype=np.uint8).reshape(-1, 32)
+    b = np.ascontiguousarray(bounds, dtype=np.uint32)
+    if b.size and int(b[-1]) > h.shape[0]:
+        raise ValueError("bounds run past the chunk-hash list")
+    out = np.empty((max(b.size - 1, 0), 32), np.uint8)
+    if out.shape[0]:
+        check(_native.lib().zg_range_hashes(ctx.handle, h.ctypes.data, b.ctypes.data, out.shape[0], out.ctypes.data))
+    return out
+
+
 def _merkle(hashes, lens, file_mode, ctx):
     ctx = ctx or default_context()
     h = np.ascontiguousarray(hashes, dtype=np.uint8).reshape(-1, 32)
