@@ -25,7 +25,8 @@
 //   execute : 32 consecutive true sequences per step, one per lane: output positions by a warp scan of the lengths,
 //             the offset/size checks of the oracle on those positions, then literals and matches whose source
 //             precedes the step in one pass (all loads before all stores), and the matches that read the step's
-//             own output in frontier rounds.  Runs longer than 16 bytes are copied by the whole warp.
+//             own output in rounds, each as soon as the matches it reads from are done (dependency masks by
+//             binary search over the lanes).  Runs longer than 16 bytes are copied by the whole warp.
 //   serial  : frame and block headers, the last sequence of a block, stored blocks, oversized pieces and every error
 //             go through a plain one-sequence-at-a-time walker that mirrors the oracle check for check; it runs
 //             uniformly on all lanes (same instructions, no broadcasts) and feeds the same execute step.
@@ -235,6 +236,13 @@ __device__ __forceinline__ void warp_regroup(uint8_t* out, const uint8_t* tmp, u
 }
 
 
+#ifdef ZG_LZ4_PROFILE  // developer build: execute-step counters, read by tools/stage_bench.py (ZG_PROF=1)
+__device__ unsigned long long g_prof[8];  // cycles in pass 1 / long copies / match rounds; steps; rounds; pending per round; long runs
+#define ZG_PF(i, v) do { if ((threadIdx.x & 31) == 0) atomicAdd(&g_prof[i], (unsigned long long)(v)); } while (0)
+#else
+#define ZG_PF(i, v)
+#endif
+
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     const uint32_t sa = (uint32_t)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
@@ -339,23 +347,38 @@ __device__ __noinline__ Hop spec_hop_general(const uint8_t* src, const uint8_t* 
     return h;
 }
 
-// The matches of up to 32 consecutive sequences (one per lane, stream order, ml = 0: none) whose sources may lie
-// in the output of those same sequences.  Everything below the first of them is final.  Each round copies the
-// first pending match and every other one whose source ends below it -- the frontier, below which all bytes are
-// final -- so most steps finish in one or two rounds.
+// The matches of up to 32 sequences in stream order, one per lane (ml = 0: none), whose sources may lie in the
+// output of those same sequences; everything else they read is final.  md (where the match goes) ascends with the
+// lane and the ranges [md, md + ml) are disjoint, so the lanes that write what lane i reads are a contiguous run
+// jlo .. jhi-1: jlo = number of ranges that end at or before the source, jhi = number that start before its end
+// (two 5-step binary searches by shuffle).  A match is copied as soon as none of those is still pending, so the
+// number of rounds is the depth of the dependency chains (1-3), not the number of matches.
 __device__ __forceinline__ void match_rounds(uint8_t* lz, uint32_t md, uint32_t ml, uint32_t off, uint32_t lane) {
     uint8_t* mp = lz + md;
+    uint32_t pm = __ballot_sync(kFull, ml != 0);
+    if (!pm) return;
+    const uint32_t s = md - off, e = min(s + ml, md), endv = md + ml;
+    uint32_t jlo = 0, jhi = 0;
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+        const uint32_t bj = __shfl_sync(kFull, endv, jlo + step - 1);
+        const uint32_t aj = __shfl_sync(kFull, md, jhi + step - 1);
+        if (bj <= s) jlo += step;
+        if (aj < e) jhi += step;
+    }
+    const uint32_t dep = jhi > jlo ? ((1u << jhi) - 1u) & ~((1u << jlo) - 1u) : 0u;  // jhi <= lane: never the lane itself
     for (;;) {
-        const uint32_t pm = __ballot_sync(kFull, ml != 0);
-        if (!pm) break;
+        ZG_PF(4, 1);
+        ZG_PF(5, __popc(pm));
         __syncwarp();
-        const int f = __ffs(pm) - 1;
-        const uint32_t f_md = __shfl_sync(kFull, md, f), f_ml = __shfl_sync(kFull, ml, f), f_off = __shfl_sync(kFull, off, f);
-        if (f_ml > kShort) {  // long match: first in line, whole warp
-            warp_match(lz + f_md, f_off, f_ml, lane);
-            if ((int)lane == f) ml = 0;
+        const bool ready = ml != 0 && (dep & pm) == 0;
+        uint32_t lm = __ballot_sync(kFull, ready && ml > kShort);  // long matches: whole warp, one after the other
+        while (lm) {
+            const int l = __ffs(lm) - 1;
+            lm &= lm - 1;
+            warp_match(lz + __shfl_sync(kFull, md, l), __shfl_sync(kFull, off, l), __shfl_sync(kFull, ml, l), lane);
         }
-        const bool go = ml != 0 && ml <= kShort && ((int)lane == f || md - off + ml <= f_md);
+        const bool go = ready && ml <= kShort;
         const bool fast = go && off >= ml;
         uint32_t x[4];
         load16<false>(mp - off, fast ? ml : 0u, x);
@@ -364,7 +387,9 @@ __device__ __forceinline__ void match_rounds(uint8_t* lz, uint32_t md, uint32_t 
             const uint8_t* g = mp - off;
             for (uint32_t b = 0; b < ml; b++) mp[b] = g[b];
         }
-        if (go) ml = 0;
+        if (ready) ml = 0;
+        pm = __ballot_sync(kFull, ml != 0);
+        if (!pm) break;
     }
 }
 
@@ -372,12 +397,15 @@ __device__ __forceinline__ void match_rounds(uint8_t* lz, uint32_t md, uint32_t 
 // (lanes without a sequence pass lit = ml = 0).  dst is the sequence's output position, op0 the position of the
 // step's first byte; everything below op0 is final.  Pass 1 copies every literal run and every match whose source
 // lies wholly below op0 (most of them) with all loads of the step in flight together; the matches that read the
-// step's own output follow, 32 at a time, in frontier rounds.
+// step's own output follow in match_rounds.
 template <int NP>
 __device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint32_t op0, const uint32_t (&lit_src)[NP],
                                            const uint32_t (&lit)[NP], uint32_t (&ml)[NP], const uint32_t (&off)[NP],
                                            const uint32_t (&dst)[NP], uint32_t lane) {
     __syncwarp();
+#ifdef ZG_LZ4_PROFILE
+    const long long pt0 = clock64();
+#endif
     uint32_t x[NP][4], y[NP][4], n[NP], k[NP];
     bool old[NP];
 #pragma unroll
@@ -395,9 +423,15 @@ __device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint
     for (int q = 0; q < NP; q++) store16(lz + dst[q], n[q], x[q]);
 #pragma unroll
     for (int q = 0; q < NP; q++) store16(lz + dst[q] + lit[q], k[q], y[q]);
+#ifdef ZG_LZ4_PROFILE
+    const long long pt1 = clock64();
+    ZG_PF(0, pt1 - pt0);
+    ZG_PF(3, 1);
+#endif
 #pragma unroll
     for (int q = 0; q < NP; q++) {
         uint32_t lm = __ballot_sync(kFull, lit[q] > kShort);  // long literal runs: whole-warp copies
+        ZG_PF(6, __popc(lm));
         while (lm) {
             const int l = __ffs(lm) - 1;
             lm &= lm - 1;
@@ -405,6 +439,7 @@ __device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint
                              __shfl_sync(kFull, lit[q], l), lane);
         }
         lm = __ballot_sync(kFull, old[q] && ml[q] > kShort);  // long matches from below the step: the same
+        ZG_PF(7, __popc(lm));
         while (lm) {
             const int l = __ffs(lm) - 1;
             lm &= lm - 1;
@@ -413,8 +448,15 @@ __device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint
         }
         if (old[q]) ml[q] = 0;
     }
+#ifdef ZG_LZ4_PROFILE
+    const long long pt2 = clock64();
+    ZG_PF(1, pt2 - pt1);
+#endif
 #pragma unroll
     for (int q = 0; q < NP; q++) match_rounds(lz, dst[q] + lit[q], ml[q], off[q], lane);
+#ifdef ZG_LZ4_PROFILE
+    ZG_PF(2, clock64() - pt2);
+#endif
 }
 
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
@@ -846,6 +888,13 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
 }
 
 }  // namespace
+
+#ifdef ZG_LZ4_PROFILE
+extern "C" __attribute__((visibility("default"))) void zg_lz4_profile_read(unsigned long long* out8, int reset) {
+    cudaMemcpyFromSymbol(out8, g_prof, sizeof(g_prof));
+    if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(g_prof, z, sizeof(z)); }
+}
+#endif
 
 void fill_decode_order(ChunkDesc* chunks, size_t n) {
     std::vector<uint32_t> idx(n);
