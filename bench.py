@@ -337,6 +337,20 @@ def main():
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(dom)
     except (OSError, ValueError):
         pass
+    # The decoder is bound by instruction issue, not by HBM: put its launch time against the issue floor of the warp
+    # instructions ncu counted for this workload (profiles/traffic.json), 4 schedulers per SM at the observed clock.
+    lz4_issue = None
+    try:
+        n_inst = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get("lz4_decode_warp_instructions")
+        if n_inst:
+            n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+            mhz = (clocks or {}).get("sm_mhz") or float(peaks.get("sm_max_mhz", 1965.0))
+            floor_ms = n_inst / (4.0 * n_sm * mhz * 1e6) * 1e3
+            lz4_issue = {"warp_instructions": int(n_inst), "issue_floor_ms": round(floor_ms, 4),
+                         "frac_of_issue_floor": round(floor_ms / (stages["lz4_decode"] * 1e3), 4),
+                         "note": "smsp__inst_executed.sum of one launch (ncu, profiles/r1_ncu_decode_spec.txt) / (4 schedulers x SMs x SM clock)"}
+    except (OSError, ValueError):
+        pass
     from oracle import xet_oracle as oz
     compressions = sum(oz.blake3_compressions(int(n)) for n in lens)
     int_ops = compressions * INT_OPS_PER_COMPRESSION
@@ -353,6 +367,7 @@ def main():
                 "algorithmic_bytes_per_launch": int(alg[dom]), "avg_launch_ms": round(stages[dom] * 1e3, 4),
                 "stages": {s: {"ms": round(t * 1e3, 4), "alg_GBps": round(alg[s] / t / 1e9, 2),
                                "uncompressed_GBps": round(total / t / 1e9, 2)} for s, t in stages.items()},
+                "lz4_issue": lz4_issue,
                 "blake3_alu": {"compressions": int(compressions), "int_ops": int(int_ops),
                                "achieved_Tops": round(int_ops / stages["blake3_hash"] / 1e12, 3),
                                "measured_pipe_peaks_Tops": {"alu": round(g_alu.value / 1e3, 2), "fma_imad": round(g_fma.value / 1e3, 2),

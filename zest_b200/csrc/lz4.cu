@@ -65,6 +65,9 @@ constexpr uint32_t kJoinHops = 64;    // sequences a chain may walk beyond its s
 #define ZG_POOL 704
 #endif
 constexpr uint32_t kPool = ZG_POOL;       // records per round, all lanes together (slots are handed out per iteration)
+#ifndef ZG_PREROLL
+#define ZG_PREROLL 32     // run-up bytes in front of each speculative segment (0: none)
+#endif
 constexpr uint32_t kSpanMax = 32 * kSeg;
 constexpr uint32_t kWinBytes = 2304;  // staged stream bytes: alignment slack + span + >= 100 bytes beyond it
 constexpr int32_t kNotTrue = INT32_MIN;
@@ -539,6 +542,25 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
             const uint32_t lt = (1u << lane) - 1;
             const uint32_t segend = min(pos + kSeg, spanend);
             bool run = lane < nseg;  // chain alive (not stopped by something unusual)
+#if ZG_PREROLL > 0
+            // Run-up: lanes 1.. start up to ZG_PREROLL bytes before their segment and walk into it without recording,
+            // so that most chains are already on true boundaries when their segment begins and the chain before them
+            // joins within a hop or two (fewer join iterations, fewer speculative records in the pool).
+            {
+                const uint32_t seg0 = pos;
+                uint32_t pp = lane * kSeg > ZG_PREROLL ? seg0 - ZG_PREROLL : ip;
+#pragma unroll 1
+                for (uint32_t it = 0; it < ZG_PREROLL / 2; it++) {
+                    const bool act = run && lane != 0 && pp < seg0;
+                    if (!__any_sync(kFull, act)) break;
+                    if (act) {
+                        const Hop h = spec_hop(src, win, wofs, pp, bend);
+                        pp = h.ok ? h.nip : seg0;  // a dead run-up falls back to the segment's first byte
+                    }
+                }
+                if (lane != 0 && pp > seg0) pos = pp;
+            }
+#endif
 #pragma unroll 1
             for (uint32_t it = 0; it < kCap; it++) {
                 const bool act = run && pos < segend;
