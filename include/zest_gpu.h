@@ -210,6 +210,29 @@ ZG_API size_t zg_dev_cdc_scratch_bytes(uint64_t len);
 ZG_API int zg_dev_cdc(zg_ctx* ctx, const uint8_t* d_data, uint64_t len, uint64_t* d_ends, uint64_t cap, uint64_t* d_n_out,
                void* d_scratch, size_t scratch_bytes, void* stream);
 
+/* ---- dedup index --------------------------------------------------------------------------- */
+/* A table in HBM from Xet chunk hash to a caller-defined 64-bit location (for instance xorb number << 32 | chunk
+ * index).  On the seed/dedup path it answers for a whole batch of hashes what zest asks one file-system probe at a
+ * time -- storage.hasChunk (src/storage.zig:137) and the XorbRegistry scan (src/storage.zig:145-228) -- and what
+ * xet-core keeps in its global dedup table; the hashes come from zg_cdc_hash and can stay on the device
+ * (zg_dev_dedup_*).  Per hash the table keeps the smallest location ever inserted for it ("first seen" when
+ * locations grow); was_new[i] = 1 iff the hash was absent before this call and occurrence i carries the location
+ * kept.  max_entries fixes the size (the table is kept at most half full; 52 bytes per slot): inserting more returns
+ * ZG_ERR_CAPACITY.  Calls on one table must not overlap (the host-buffer calls serialise themselves; device calls
+ * are ordered by the caller's stream); errors of device calls (table full, two different hashes agreeing in their
+ * 64 tag bits) surface at the next zg_dedup_count / host-buffer insert.  ZG_DEDUP_MISSING is not a valid location. */
+typedef struct zg_dedup zg_dedup;
+#define ZG_DEDUP_MISSING (~(uint64_t)0)
+ZG_API int zg_dedup_create(zg_ctx* ctx, size_t max_entries, zg_dedup** out);
+ZG_API void zg_dedup_destroy(zg_dedup* t);
+ZG_API int zg_dedup_insert(zg_dedup* t, const uint8_t* hashes /* n x 32 */, const uint64_t* locations, size_t n,
+                    uint8_t* was_new /* n bytes or NULL */);
+ZG_API int zg_dedup_lookup(zg_dedup* t, const uint8_t* hashes, size_t n, uint64_t* locations /* ZG_DEDUP_MISSING: absent */);
+ZG_API int zg_dedup_count(zg_dedup* t, uint64_t* entries);
+ZG_API int zg_dev_dedup_insert(zg_dedup* t, const uint8_t* d_hashes, const uint64_t* d_locations, size_t n, uint8_t* d_was_new,
+                        void* stream);
+ZG_API int zg_dev_dedup_lookup(zg_dedup* t, const uint8_t* d_hashes, size_t n, uint64_t* d_locations, void* stream);
+
 /* ---- measurement aid -------------------------------------------------------------------------------------------- */
 /* Measured peak of the SM's integer pipes in Gop/s (thread-level 32-bit operations): the ALU pipe (LOP3 / SHF / IADD3),
  * the FMA pipe (IMAD) and both together.  bench.py reports the BLAKE3 kernel against these (SURVEY.md 8d asks for a

@@ -363,6 +363,95 @@ def test_range_hashes(ctx, oracle, vectors):
         z.range_hashes(hashes, [5, 2], ctx=ctx)
 
 
+def _dict_insert(table, hashes, locs):
+    """Reference semantics of DedupIndex.insert on a Python dict."""
+    keys = [h.tobytes() for h in hashes]
+    fresh = {k for k in keys if k not in table}
+    for k, l in zip(keys, locs):
+        table[k] = min(table.get(k, 1 << 64), int(l))
+    return np.array([k in fresh and table[k] == int(l) for k, l in zip(keys, locs)])
+
+
+def test_dedup_index_vs_dict(ctx):
+    """Insert / lookup against a dict: duplicates inside a batch and across batches, absent keys, keys that share
+    their slot word or their tag word with a stored key, locations that are not monotonic."""
+    rng = np.random.default_rng(31)
+    idx = z.DedupIndex(200_000, ctx)
+    table = {}
+    pool = rng.integers(0, 256, (60_000, 32), dtype=np.uint8)
+    pool[1000:1100, :8] = pool[0, :8]            # same home slot as key 0: a probe chain
+    pool[2000:2050, 8:16] = pool[1, 8:16]        # same tag as key 1, different slot word
+    for b in range(6):
+        pick = rng.integers(0, pool.shape[0], 30_000)
+        hashes = pool[pick]
+        locs = rng.integers(0, 1 << 40, pick.size).astype(np.uint64)
+        got = idx.insert(hashes, locs)
+        want = _dict_insert(table, hashes, locs)
+        assert (got == want).all(), b
+        assert len(idx) == len(table)
+    probe = np.concatenate([pool[::7], rng.integers(0, 256, (5000, 32), dtype=np.uint8)])
+    got = idx.lookup(probe)
+    want = np.array([table.get(h.tobytes(), int(z.dedup.MISSING)) for h in probe], dtype=np.uint64)
+    assert (got == want).all()
+    assert idx.lookup(np.zeros((0, 32), np.uint8)).size == 0
+    with pytest.raises(z.ZestGpuError):          # the reserved value is refused
+        idx.insert(pool[:1], np.array([z.dedup.MISSING], np.uint64))
+    idx.close()
+
+
+def test_dedup_index_capacity_and_real_hashes(ctx, oracle):
+    """Over-filling reports ZG_ERR_CAPACITY; chunk hashes of a file with repeated regions dedup as expected."""
+    small = z.DedupIndex(100, ctx)
+    h = np.random.default_rng(5).integers(0, 256, (400, 32), dtype=np.uint8)
+    with pytest.raises(z.ZestGpuError) as ei:
+        small.insert(h, np.arange(400, dtype=np.uint64))
+    assert ei.value.code == -10
+    small.close()
+    base = oracle.synth_random(3_000_000, 8)
+    data = np.concatenate([base, oracle.synth_random(500_000, 9), base])      # the second copy re-synchronises
+    ends, hashes, _ = z.cdc_hash(data, ctx=ctx)
+    idx = z.DedupIndex(4 * ends.size, ctx)
+    new = idx.insert(hashes, np.arange(ends.size, dtype=np.uint64))
+    uniq = len({x.tobytes() for x in hashes})
+    assert int(new.sum()) == uniq == len(idx) and uniq < ends.size - 20
+    loc = idx.lookup(hashes)
+    first = {}
+    for i, x in enumerate(hashes):
+        first.setdefault(x.tobytes(), i)
+    assert [int(v) for v in loc] == [first[x.tobytes()] for x in hashes]
+    idx.close()
+
+
+def test_dedup_device_calls(ctx):
+    """zg_dev_dedup_insert / lookup on device-resident hashes (as they come out of zg_dev_hash_chunks) give what
+    the host-buffer calls give."""
+    import ctypes as C
+    import torch
+    from zest_b200 import _native
+    L = _native.lib()
+    rng = np.random.default_rng(77)
+    hashes = rng.integers(0, 256, (50_000, 32), dtype=np.uint8)
+    hashes[25_000:] = hashes[:25_000]                       # every hash twice
+    locs = np.arange(50_000, dtype=np.uint64)[::-1].copy()  # descending: the later occurrence has the smaller location
+    dev = torch.device("cuda", ctx.device)
+    d_h = torch.from_numpy(hashes).to(dev)
+    d_l = torch.from_numpy(locs.view(np.int64)).to(dev)
+    d_new = torch.zeros(50_000, dtype=torch.uint8, device=dev)
+    d_out = torch.zeros(50_000, dtype=torch.int64, device=dev)
+    idx = z.DedupIndex(60_000, ctx)
+    sp = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    _native.check(L.zg_dev_dedup_insert(idx.handle, d_h.data_ptr(), d_l.data_ptr(), 50_000, d_new.data_ptr(), sp))
+    _native.check(L.zg_dev_dedup_lookup(idx.handle, d_h.data_ptr(), 50_000, d_out.data_ptr(), sp))
+    torch.cuda.synchronize(dev)
+    assert len(idx) == 25_000
+    new = d_new.cpu().numpy().astype(bool)
+    assert not new[:25_000].any() and new[25_000:].all()   # the occurrence with the smaller location is the one kept
+    got = d_out.cpu().numpy().view(np.uint64)
+    assert (got[:25_000] == locs[25_000:]).all() and (got[25_000:] == locs[25_000:]).all()
+    assert (idx.lookup(hashes) == got).all()
+    idx.close()
+
+
 # ------------------------------------------------------------------------------------------------ CDC
 @pytest.mark.parametrize("name", ["seed0_1MiB", "seed1_8MiB", "zeros_1MiB", "seed1_next_8191", "seed1_next_8192",
                                   "bf16_seed2_4MiB", "zipf_seed3_2MiB", "hello_world", "empty"])

@@ -100,3 +100,16 @@ def test_xetblob_footer_matches_xet_core(vectors, name):
     hashes, _, xorb_hash = footer_chunk_hashes(raw)
     ix = z.xorb_index(stream)
     assert z.xorb_footer(xorb_hash, hashes, ix.clen, ix.ulen) == raw[len(stream):]
+
+
+def test_dedup_shard_of_is_balanced_and_stable():
+    """Owner GPU of a chunk hash when the dedup index is split across GPUs: a pure function of the hash, uniform."""
+    import numpy as np
+    from zest_b200.dedup import shard_of
+    h = np.random.default_rng(3).integers(0, 256, (80_000, 32), dtype=np.uint8)
+    for n in (1, 2, 4, 8):
+        s = shard_of(h, n)
+        assert s.min() >= 0 and s.max() < n
+        counts = np.bincount(s, minlength=n)
+        assert counts.min() > 0.9 * h.shape[0] / n
+        assert (shard_of(h[::-1], n)[::-1] == s).all()

@@ -27,6 +27,8 @@ SYMBOLS = [
     "zg_dev_decode_scratch_bytes", "zg_dev_decode_chunks", "zg_dev_merkle_scratch_bytes", "zg_dev_merkle",
     "zg_dev_verify_scratch_bytes", "zg_dev_verify_xorbs", "zg_dev_cdc_scratch_bytes", "zg_dev_cdc", "zg_get_stats",
     "zg_chunk_order", "zg_dev_hash_chunks_static", "zg_xorb_footer_bytes", "zg_xorb_footer", "zg_dev_int_pipe_peak",
+    "zg_dedup_create", "zg_dedup_destroy", "zg_dedup_insert", "zg_dedup_lookup", "zg_dedup_count", "zg_dev_dedup_insert",
+    "zg_dev_dedup_lookup",
 ]
 
 
@@ -86,6 +88,14 @@ def lib() -> C.CDLL:
         L.zg_hash_chunks.argtypes = [vp, vp, vp, sz, vp, vp]
         L.zg_merkle_root.argtypes = [vp, vp, vp, sz, i32, vp]
         L.zg_range_hashes.argtypes = [vp, vp, vp, sz, vp]
+        L.zg_dedup_create.argtypes = [vp, sz, C.POINTER(vp)]
+        L.zg_dedup_destroy.argtypes = [vp]
+        L.zg_dedup_destroy.restype = None
+        L.zg_dedup_insert.argtypes = [vp, vp, vp, sz, vp]
+        L.zg_dedup_lookup.argtypes = [vp, vp, sz, vp]
+        L.zg_dedup_count.argtypes = [vp, vp]
+        L.zg_dev_dedup_insert.argtypes = [vp, vp, vp, sz, vp, vp]
+        L.zg_dev_dedup_lookup.argtypes = [vp, vp, sz, vp, vp]
         L.zg_cdc.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz)]
         L.zg_cdc_hash.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz), vp, vp]
         L.zg_dev_hash_scratch_bytes.argtypes = [u64, sz]

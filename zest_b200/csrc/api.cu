@@ -915,6 +915,128 @@ void zg_chunk_order(zg_chunk_desc* descs, size_t n) {
     if (descs && n) fill_decode_order(reinterpret_cast<ChunkDesc*>(descs), n);
 }
 
+// ---- dedup index (dedup.cu) ----------------------------------------------------------------------------------
+struct zg_dedup {
+    zg_ctx* ctx = nullptr;
+    void* mem = nullptr;
+    DedupView v{};
+    uint64_t max_entries = 0;
+    std::mutex mu;               // host-buffer inserts and lookups on one table are serialised
+    std::atomic<uint32_t> epoch{0};
+};
+
+static int dedup_check_counters(zg_dedup* t, const unsigned long long c[3]) {
+    if (c[2]) return fail(ZG_ERR_LIMIT, "dedup index: %llu chunk hashes agree in 64 tag bits with a different stored hash", c[2]);
+    if (c[1] || c[0] > t->max_entries) return fail(ZG_ERR_CAPACITY, "dedup index holds %llu entries, created for %llu", c[0], (unsigned long long)t->max_entries);
+    return ZG_OK;
+}
+
+int zg_dedup_create(zg_ctx* ctx, size_t max_entries, zg_dedup** out) {
+    int r = check_ctx(ctx);
+    if (r) return r;
+    if (!out || max_entries == 0) return fail(ZG_ERR_INVALID_ARG, "null argument or zero capacity");
+    if (max_entries > (1ull << 36)) return fail(ZG_ERR_LIMIT, "dedup index too large");
+    uint64_t slots = 64;
+    while (slots < 2 * (uint64_t)max_entries) slots <<= 1;  // at most half full
+    std::unique_ptr<zg_dedup> t(new zg_dedup);
+    t->ctx = ctx;
+    t->max_entries = max_entries;
+    cudaError_t e = cudaMalloc(&t->mem, dedup_table_bytes(slots));
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return fail(ZG_ERR_OOM, "cudaMalloc(%zu): %s", dedup_table_bytes(slots), cudaGetErrorString(e)); }
+    t->v = dedup_view(t->mem, slots);
+    LaneGuard g(ctx);
+    e = dedup_clear(t->v, g.l->st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g.l->st);
+    if (e != cudaSuccess) { cudaFree(t->mem); return cuda_fail(e, "dedup clear"); }
+    *out = t.release();
+    return ZG_OK;
+}
+
+void zg_dedup_destroy(zg_dedup* t) {
+    if (!t) return;
+    if (t->mem) cudaFree(t->mem);
+    delete t;
+}
+
+int zg_dedup_insert(zg_dedup* t, const uint8_t* hashes, const uint64_t* locations, size_t n, uint8_t* was_new) {
+    if (!t) return fail(ZG_ERR_INVALID_ARG, "null table");
+    int r = check_ctx(t->ctx);
+    if (r) return r;
+    if (n == 0) return ZG_OK;
+    if (!hashes || !locations) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    for (size_t i = 0; i < n; i++)
+        if (locations[i] == ZG_DEDUP_MISSING) return fail(ZG_ERR_INVALID_ARG, "location %zu is the reserved value", i);
+    std::lock_guard<std::mutex> lk(t->mu);
+    LaneGuard g(t->ctx);
+    Lane& L = *g.l;
+    const size_t o_loc = align_up(32 * n, 256), o_new = o_loc + align_up(8 * n, 256), total = o_new + align_up(n, 256);
+    if ((r = L.meta.ensure(total, L.st)) || (r = L.hres.ensure(align_up(n, 256) + 64, L.st))) return r;
+    uint8_t* d = static_cast<uint8_t*>(L.meta.p);
+    CU(cudaMemcpyAsync(d, hashes, 32 * n, cudaMemcpyHostToDevice, L.st));
+    CU(cudaMemcpyAsync(d + o_loc, locations, 8 * n, cudaMemcpyHostToDevice, L.st));
+    CU(launch_dedup_insert(t->v, d, reinterpret_cast<const uint64_t*>(d + o_loc), n, ++t->epoch, d + o_new, L.st));
+    uint8_t* hr = static_cast<uint8_t*>(L.hres.p);
+    CU(cudaMemcpyAsync(hr, t->v.counters, 24, cudaMemcpyDeviceToHost, L.st));
+    CU(cudaMemcpyAsync(hr + 64, d + o_new, n, cudaMemcpyDeviceToHost, L.st));
+    CU(cudaStreamSynchronize(L.st));
+    if (was_new) memcpy(was_new, hr + 64, n);
+    t->ctx->kernels += 2;
+    t->ctx->h2d += 40 * n;
+    t->ctx->d2h += n + 24;
+    unsigned long long c[3];
+    memcpy(c, hr, 24);
+    return dedup_check_counters(t, c);
+}
+
+int zg_dedup_lookup(zg_dedup* t, const uint8_t* hashes, size_t n, uint64_t* locations) {
+    if (!t) return fail(ZG_ERR_INVALID_ARG, "null table");
+    int r = check_ctx(t->ctx);
+    if (r) return r;
+    if (n == 0) return ZG_OK;
+    if (!hashes || !locations) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(t->mu);
+    LaneGuard g(t->ctx);
+    Lane& L = *g.l;
+    const size_t o_out = align_up(32 * n, 256);
+    if ((r = L.meta.ensure(o_out + 8 * n, L.st))) return r;
+    uint8_t* d = static_cast<uint8_t*>(L.meta.p);
+    CU(cudaMemcpyAsync(d, hashes, 32 * n, cudaMemcpyHostToDevice, L.st));
+    CU(launch_dedup_lookup(t->v, d, n, reinterpret_cast<uint64_t*>(d + o_out), L.st));
+    CU(cudaMemcpyAsync(locations, d + o_out, 8 * n, cudaMemcpyDeviceToHost, L.st));
+    CU(cudaStreamSynchronize(L.st));
+    t->ctx->kernels += 1;
+    t->ctx->h2d += 32 * n;
+    t->ctx->d2h += 8 * n;
+    return ZG_OK;
+}
+
+int zg_dedup_count(zg_dedup* t, uint64_t* entries) {
+    if (!t || !entries) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(t->mu);
+    unsigned long long c[3];
+    CU(cudaMemcpy(c, t->v.counters, 24, cudaMemcpyDeviceToHost));  // waits for all earlier work on the device
+    *entries = c[0];
+    return dedup_check_counters(t, c);
+}
+
+int zg_dev_dedup_insert(zg_dedup* t, const uint8_t* d_hashes, const uint64_t* d_locations, size_t n, uint8_t* d_was_new, void* stream) {
+    if (!t) return fail(ZG_ERR_INVALID_ARG, "null table");
+    if (n == 0) return ZG_OK;
+    if (!d_hashes || !d_locations) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    CU(launch_dedup_insert(t->v, d_hashes, d_locations, n, ++t->epoch, d_was_new, static_cast<cudaStream_t>(stream)));
+    t->ctx->kernels += 2;
+    return ZG_OK;
+}
+
+int zg_dev_dedup_lookup(zg_dedup* t, const uint8_t* d_hashes, size_t n, uint64_t* d_locations, void* stream) {
+    if (!t) return fail(ZG_ERR_INVALID_ARG, "null table");
+    if (n == 0) return ZG_OK;
+    if (!d_hashes || !d_locations) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    CU(launch_dedup_lookup(t->v, d_hashes, n, d_locations, static_cast<cudaStream_t>(stream)));
+    t->ctx->kernels += 1;
+    return ZG_OK;
+}
+
 int zg_get_stats(zg_ctx* ctx, zg_stats* out) {
     if (!ctx || !out) return fail(ZG_ERR_INVALID_ARG, "null argument");
     out->calls = ctx->calls; out->kernels_launched = ctx->kernels; out->h2d_bytes = ctx->h2d; out->d2h_bytes = ctx->d2h;

@@ -64,4 +64,21 @@ size_t cdc_scratch_bytes(uint64_t len);
 cudaError_t launch_cdc(const uint8_t* data, uint64_t len, uint64_t* ends, uint64_t cap, uint64_t* n_out,
                        void* scratch, size_t scratch_bytes, cudaStream_t st);
 
+// ---------------------------------------------------------------------------------------------- dedup index
+struct DedupView {  // the table's arrays inside one device allocation of dedup_table_bytes(slots)
+    uint64_t slots;                 // power of two, >= 64
+    unsigned long long* tags;       // hash bytes 8..15 with the top bit set; 0 = empty
+    unsigned long long* locs;       // smallest location inserted for the slot's hash
+    uint8_t* keys;                  // 32 bytes per slot
+    uint32_t* born;                 // insert batch that created the slot
+    unsigned long long* counters;   // [0] entries, [1] table-full flag, [2] tag matches whose key differed
+};
+size_t dedup_table_bytes(uint64_t slots);
+DedupView dedup_view(void* base, uint64_t slots);
+cudaError_t dedup_clear(const DedupView& v, cudaStream_t st);
+// hashes: n x 32 bytes, locations: n u64, was_new: n bytes or null -- all device pointers.
+cudaError_t launch_dedup_insert(const DedupView& v, const uint8_t* hashes, const uint64_t* locations, uint64_t n,
+                                uint32_t epoch, uint8_t* was_new, cudaStream_t st);
+cudaError_t launch_dedup_lookup(const DedupView& v, const uint8_t* hashes, uint64_t n, uint64_t* out, cudaStream_t st);
+
 }  // namespace zg
