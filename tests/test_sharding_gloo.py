@@ -53,3 +53,79 @@ def test_two_rank_sharding():
     assert v0 == v1 and sorted(p0 + p1) == list(range(7)) and not set(p0) & set(p1)
     assert [int(x == 1) for x in v0] == [1, 1, 1, 1, 0, 1, 1]
     assert t0 == t1 and m0 == m1 == 1.5
+
+
+class _DictShard:
+    """CPU stand-in for the device shard of ShardedDedupIndex (test infrastructure: same semantics as dedup.cu)."""
+
+    def __init__(self):
+        self.table = {}
+
+    def insert_t(self, hashes_t, locs_t):
+        import torch
+        keys = [bytes(h.tolist()) for h in hashes_t]
+        fresh = {k for k in keys if k not in self.table}
+        for k, l in zip(keys, locs_t.tolist()):
+            self.table[k] = min(self.table.get(k, 1 << 62), int(l))
+        return torch.tensor([int(k in fresh and self.table[k] == int(l)) for k, l in zip(keys, locs_t.tolist())], dtype=torch.uint8)
+
+    def lookup_t(self, hashes_t):
+        import torch
+        return torch.tensor([self.table.get(bytes(h.tolist()), -1) for h in hashes_t], dtype=torch.int64)
+
+
+def _dedup_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    import torch
+    from zest_b200 import distributed as zd
+    from zest_b200.dedup import ShardedDedupIndex, shard_of
+    r, w, _ = zd.init_from_env("gloo")
+    shard = _DictShard()
+    idx = ShardedDedupIndex(0, local=shard)
+    rng = np.random.default_rng(100)                       # same pool on both ranks
+    pool = rng.integers(0, 256, (4000, 32), dtype=np.uint8)
+    mine = np.random.default_rng(r).integers(0, 4000, 3000)  # overlapping picks, different per rank
+    hashes = torch.from_numpy(pool[mine])
+    locs = torch.from_numpy((mine.astype(np.int64) << 8) | r)   # location encodes (pool index, inserting rank)
+    new = idx.insert(hashes, locs)
+    zd.barrier()
+    found = idx.lookup(torch.from_numpy(pool))
+    owned_ok = all(int(shard_of(np.frombuffer(k, np.uint8), w)[0]) == r for k in shard.table)
+    q.put((r, mine.tolist(), new.tolist(), found.tolist(), len(shard.table), owned_ok))
+    zd.shutdown()
+
+
+def test_two_rank_sharded_dedup_index():
+    """Routing of the split dedup index over two gloo ranks: every hash lands on its owner, answers come back in
+    input order, both ranks see the same global answer, and it equals a single dict fed with both ranks' batches."""
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_dedup_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in ps)
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, m0, n0, f0, c0, ok0), (_, m1, n1, f1, c1, ok1) = res
+    assert ok0 and ok1 and f0 == f1
+    want = {}
+    for r, m in ((0, m0), (1, m1)):
+        for i in m:
+            want[i] = min(want.get(i, 1 << 62), (i << 8) | r)
+    assert c0 + c1 == len(want)
+    assert f0 == [want.get(i, -1) for i in range(4000)]
+    # was_new: exactly one occurrence per distinct hash overall claims it (the one whose location was kept);
+    # duplicates of a hash inside one rank's batch carry the same location and all report it
+    kept = {}
+    for r, m, n in ((0, m0, n0), (1, m1, n1)):
+        for i, flag in zip(m, n):
+            if flag:
+                kept.setdefault(i, set()).add(r)
+    assert set(kept) == set(want) and all(len(v) == 1 for v in kept.values())
+    assert all(((want[i] & 0xff) in v) for i, v in kept.items())
