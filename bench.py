@@ -10,7 +10,8 @@ GPU.  Rank 0 prints ONE JSON line.
               per step on torch's current stream, CUDA events, max over ranks.  GB = 1e9 uncompressed bytes.
   e2e         same metric through the reference-facing call (zg_verify_xorbs) with pinned HOST buffers: host walk
               of the chunk stream, H2D of the compressed bytes, kernels, D2H of roots + verdicts, all inside the
-              timed region.
+              timed region.  `e2e.two_callers` is the same K calls issued by two host threads (how zest would call
+              it); the one-caller figure stays `e2e.value`.
   roofline    the dominant kernel of the step (timed alone with CUDA events, same inputs), algorithmic bytes /
               time against the measured HBM copy bandwidth in MEASURED_PEAKS.json; `stages` lists every kernel;
               `blake3_alu` reports the hash kernel against the integer-ALU roof.
@@ -279,8 +280,31 @@ def main():
     torch.cuda.synchronize(); zd.barrier()
     t_e2e = zd.reduce_max(time.perf_counter() - t0)
     s1 = ctx.stats()
-    clocks = sampler.stop() if rank == 0 else None
     e2e_val = all_bytes * K / t_e2e / 1e9
+    # The same K calls issued by two host threads (zest runs up to 128 download tasks at once,
+    # src/parallel_download.zig:117): the tail of one call -- its last chunks are a serial chain of ~2 ms after the
+    # last byte has arrived -- then overlaps the copies of the next.  Reported beside the one-caller figure, which
+    # stays the headline.
+    import threading
+    nxt, lock = [0], threading.Lock()
+
+    def caller():
+        while True:
+            with lock:
+                if nxt[0] >= K:
+                    return
+                nxt[0] += 1
+            step_e2e()
+    torch.cuda.synchronize(); zd.barrier()
+    t0 = time.perf_counter()
+    ths = [threading.Thread(target=caller) for _ in range(2)]
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    torch.cuda.synchronize(); zd.barrier()
+    t_e2e2 = zd.reduce_max(time.perf_counter() - t0)
+    clocks = sampler.stop() if rank == 0 else None
     # what the link alone does: the same compressed bytes, pinned host -> device, nothing else (bounds e2e from above)
     pin_t = torch.from_numpy(comp_host[:cpos])
     for _ in range(2):
@@ -393,6 +417,7 @@ def main():
                 "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) // K),
                 "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) // K),
                 "h2d_GBps": round((s1["h2d_bytes"] - s0["h2d_bytes"]) / t_e2e / 1e9, 2),
+                "two_callers": {"value": round(all_bytes * K / t_e2e2 / 1e9, 3), "ms_per_step": round(t_e2e2 / K * 1e3, 3)},
                 "h2d_link_GBps": round(link_gbps, 2),
                 "link_bound_GBps_uncompressed": round(link_gbps * total / comp_bytes, 2)},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
