@@ -369,7 +369,8 @@ __device__ __forceinline__ void match_rounds(uint8_t* lz, uint32_t md, uint32_t 
         if (bj <= s) jlo += step;
         if (aj < e) jhi += step;
     }
-    const uint32_t dep = jhi > jlo ? ((1u << jhi) - 1u) & ~((1u << jlo) - 1u) : 0u;  // jhi <= lane: never the lane itself
+    // jhi <= lane for ascending md; the final mask keeps the lowest pending lane ready (progress) whatever the input
+    const uint32_t dep = (jhi > jlo ? ((1u << jhi) - 1u) & ~((1u << jlo) - 1u) : 0u) & ((1u << lane) - 1u);
     for (;;) {
         ZG_PF(4, 1);
         ZG_PF(5, __popc(pm));
