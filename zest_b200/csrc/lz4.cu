@@ -7,7 +7,7 @@
 // chunk gets the same error code on both sides.
 //
 // Mapping.  One warp decodes one chunk at a time (chunks are handed out longest-first through a ticket counter,
-// 20 single-warp CTAs per SM).  LZ4's token stream is serial, and on real Xet data the sequences are tiny (text:
+// 24 single-warp CTAs per SM).  LZ4's token stream is serial, and on real Xet data the sequences are tiny (text:
 // ~5,900 per 64 KiB chunk, ~11 output bytes each), so a lane-serial walk leaves 31 lanes idle and costs ~100 warp
 // instructions per sequence.  The walk is therefore SPECULATIVE and warp-wide, in rounds:
 //   parse   : the next 32 x 68 stream bytes of the block are staged in shared memory (cp.async) and cut into 32
@@ -35,7 +35,7 @@
 //
 // Roofline: HBM-bound in principle (compressed bytes in + decoded bytes out).  In practice the kernel is bound by
 // instruction issue: ~36 warp instructions per sequence (profiles/r1_ncu_decode_spec*.txt), 55 % of the issue
-// slots busy with 20 warps per SM, the rest lost to dependent-instruction and memory latency inside each chunk's
+// slots busy with 24 warps per SM, the rest lost to dependent-instruction and memory latency inside each chunk's
 // chain.  bench.py reports achieved GB/s over the algorithmic bytes.
 #include <cuda_runtime.h>
 
@@ -62,7 +62,7 @@ constexpr uint32_t kSeg = 68;         // speculative segment, stream bytes: 17 w
 constexpr uint32_t kCap = 24;         // a 68-byte segment holds at most 23 sequences
 constexpr uint32_t kJoinHops = 64;    // sequences a chain may walk beyond its segment looking for its join
 #ifndef ZG_POOL
-#define ZG_POOL 704
+#define ZG_POOL 512
 #endif
 constexpr uint32_t kPool = ZG_POOL;       // records per round, all lanes together (slots are handed out per iteration)
 #ifndef ZG_PREROLL
@@ -473,7 +473,7 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
 }
 
 #ifndef ZG_MIN_CTAS
-#define ZG_MIN_CTAS 20
+#define ZG_MIN_CTAS 24
 #endif
 __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8_t* __restrict__ comp, const ChunkDesc* __restrict__ chunks,
                                                         uint32_t n_chunks, uint8_t* out, uint8_t* tmp,
@@ -943,7 +943,7 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     cudaError_t e = cudaMemsetAsync(ticket, 0, 256, st);
     if (e != cudaSuccess) return e;
     // One warp per CTA, one chunk per warp at a time; the grid is what the machine keeps resident (shared memory
-    // allows 20 CTAs per SM) and the ticket counter feeds it, longest chunks first.  ZEST_LZ4_WARPS overrides.
+    // allows 24 CTAs per SM) and the ticket counter feeds it, longest chunks first.  ZEST_LZ4_WARPS overrides.
     static int ctas_per_sm = 0, sms = 0;  // same answer from every thread that gets here first
     if (ctas_per_sm == 0) {
         int dev = 0, occ = 0, n_sm = 0;
@@ -953,7 +953,7 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
             ctas_per_sm = occ;
         } else {
             sms = 148;
-            ctas_per_sm = 20;
+            ctas_per_sm = 24;
         }
     }
     size_t warps = (size_t)sms * ctas_per_sm;
