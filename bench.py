@@ -286,24 +286,27 @@ def main():
     # last byte has arrived -- then overlaps the copies of the next.  Reported beside the one-caller figure, which
     # stays the headline.
     import threading
-    nxt, lock = [0], threading.Lock()
 
-    def caller():
-        while True:
-            with lock:
-                if nxt[0] >= K:
-                    return
-                nxt[0] += 1
-            step_e2e()
-    torch.cuda.synchronize(); zd.barrier()
-    t0 = time.perf_counter()
-    ths = [threading.Thread(target=caller) for _ in range(2)]
-    for th in ths:
-        th.start()
-    for th in ths:
-        th.join()
-    torch.cuda.synchronize(); zd.barrier()
-    t_e2e2 = zd.reduce_max(time.perf_counter() - t0)
+    def two_caller_pass():
+        nxt, lock = [0], threading.Lock()
+
+        def caller():
+            while True:
+                with lock:
+                    if nxt[0] >= K:
+                        return
+                    nxt[0] += 1
+                step_e2e()
+        torch.cuda.synchronize(); zd.barrier()
+        t0 = time.perf_counter()
+        ths = [threading.Thread(target=caller) for _ in range(2)]
+        for th in ths:
+            th.start()
+        for th in ths:
+            th.join()
+        torch.cuda.synchronize(); zd.barrier()
+        return zd.reduce_max(time.perf_counter() - t0)
+    t_e2e2 = sorted(two_caller_pass() for _ in range(3))[1]  # median of three: host-thread scheduling makes it noisy
     clocks = sampler.stop() if rank == 0 else None
     # what the link alone does: the same compressed bytes, pinned host -> device, nothing else (bounds e2e from above)
     pin_t = torch.from_numpy(comp_host[:cpos])
