@@ -58,9 +58,15 @@ constexpr uint32_t kMaxPiece = 65535;
 #endif
 constexpr int kNP = ZG_NP;            // groups of 32 sequences per execute step
 constexpr uint32_t kSerialCap = 16;   // sequences per round of the serial walker
-constexpr uint32_t kSeg = 68;         // speculative segment, stream bytes: 17 words, so 32 lanes start in 32 banks
+#ifndef ZG_SEG
+#define ZG_SEG 68
+#endif
+#ifndef ZG_JOIN
+#define ZG_JOIN 64
+#endif
+constexpr uint32_t kSeg = ZG_SEG;       // speculative segment, stream bytes: 17 words, so 32 lanes start in 32 banks
 constexpr uint32_t kCap = 24;         // a 68-byte segment holds at most 23 sequences
-constexpr uint32_t kJoinHops = 64;    // sequences a chain may walk beyond its segment looking for its join
+constexpr uint32_t kJoinHops = ZG_JOIN;    // sequences a chain may walk beyond its segment looking for its join
 #ifndef ZG_POOL
 #define ZG_POOL 512
 #endif
