@@ -113,31 +113,3 @@ def test_dedup_shard_of_is_balanced_and_stable():
         counts = np.bincount(s, minlength=n)
         assert counts.min() > 0.9 * h.shape[0] / n
         assert (shard_of(h[::-1], n)[::-1] == s).all()
-
-
-def test_committed_bench_lines_keep_the_contract():
-    """The bench JSON lines kept under profiles/ (the ones DESIGN.md quotes) carry every key the bench contract
-    names, with consistent arithmetic: value = bytes / time, roofline.frac = achieved / peak, e2e measured with
-    host buffers (non-zero H2D bytes), launches counted."""
-    import glob
-    import json
-    import os
-    from conftest import ROOT
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r1_bench_text_v1[0-9].json")) +
-                   glob.glob(os.path.join(ROOT, "profiles", "r1_bench_text_n[248]_v1[0-9].json")))
-    assert files
-    for f in files:
-        d = json.load(open(f))
-        for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
-                  "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "clocks", "roofline"):
-            assert k in d, (f, k)
-        assert d["unit"] == "GB/s" and d["dtype"] == "u8" and d["scaling"] == "weak" and d["vs_baseline"] is None
-        assert "workload" in d["config"] and d["warmup"] >= 3 and d["gpu_launches"] > 0
-        total = d["config"]["uncompressed_bytes_per_rank"] * d["n_gpus"]
-        assert abs(d["value"] - total / (d["ms_per_step"] * 1e-3) / 1e9) / d["value"] < 0.02
-        e = d["e2e"]
-        assert e["h2d_bytes_per_step"] >= d["config"]["compressed_bytes_per_rank"] and e["d2h_bytes_per_step"] > 0
-        assert e["value"] < d["value"]
-        r = d["roofline"]
-        assert r["bound"] == "hbm" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-3
-        assert not set(d["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}

@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(kTile) hash_count_kernel(const uint64_t* __res
 }
 
 __global__ void __launch_bounds__(1024) hash_tiles_kernel(uint32_t* __restrict__ tile_sum, uint32_t n_tiles,
-                                                          uint32_t* __restrict__ total_out) {
+                                                          uint32_t slots_cap, uint32_t* __restrict__ total_out) {
     __shared__ uint32_t warp_tot[32];
     __shared__ uint32_t carry_s;
     uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -97,19 +97,31 @@ __global__ void __launch_bounds__(1024) hash_tiles_kernel(uint32_t* __restrict__
         if (i < n_tiles) tile_sum[i] = carry + warp_tot[w] + x - m;
         __syncthreads();
     }
-    if (threadIdx.x == 0) *total_out = carry_s;
+    // The leaf kernel runs min(total, slots_cap) threads: slots beyond the scratch the caller sized (lengths that
+    // add up to more than data_bytes) are never touched; the chunks that own them come out as zero hashes.
+    if (threadIdx.x == 0) {
+        total_out[0] = carry_s < slots_cap ? carry_s : slots_cap;
+        total_out[1] = carry_s;  // the last chunk's end, for the tree kernel
+    }
 }
 
 __global__ void __launch_bounds__(256) hash_map_kernel(const uint64_t* __restrict__ off,
                                                        const uint32_t* __restrict__ len, size_t n, int group_bytes,
                                                        uint32_t* __restrict__ P,
                                                        const uint32_t* __restrict__ tile_sum,
-                                                       uint32_t* __restrict__ map) {
+                                                       uint32_t slots_cap, uint32_t* __restrict__ map,
+                                                       uint4* __restrict__ out) {
     size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
     uint32_t base = P[i] + tile_sum[i / kTile];
     P[i] = base;
     uint32_t m = groups_of(chunk_len(off, len, i), group_bytes);
+    if (base > slots_cap || m > slots_cap - base) {  // does not fit the scratch: no slots, zero hash (see hash_tiles_kernel)
+        out[2 * i] = make_uint4(0, 0, 0, 0);
+        out[2 * i + 1] = make_uint4(0, 0, 0, 0);
+        for (uint32_t t = base; t < slots_cap; t++) map[t] = 0xffffffffu;  // only the first such chunk starts below the cap
+        return;
+    }
     for (uint32_t k = 0; k < m; k++) map[base + k] = (uint32_t)i;
 }
 
@@ -168,6 +180,7 @@ __global__ void __launch_bounds__(128) hash_leaf_kernel(const uint8_t* __restric
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= *total_slots) return;
     uint32_t ci = map[t];
+    if (ci == 0xffffffffu) return;  // slot of a chunk that did not fit the scratch (hash_map_kernel)
     uint32_t k = t - P[ci];
     uint64_t clen = chunk_len(off, len, ci);
     const uint8_t* base = data + off[ci];
@@ -246,7 +259,7 @@ __device__ __forceinline__ void store_cv(uint4* p, const uint32_t (&cv)[8]) {
 // SURVEY.md A.2), ROOT goes on the last parent.  Teams are packed side by side in a warp, so lanes stay busy across
 // chunks; any node count works (a 16 MiB chunk just loops).
 __global__ void __launch_bounds__(128) hash_tree_kernel(const B3Key key, const uint32_t* __restrict__ P, size_t n,
-                                                        uint32_t team, uint4* __restrict__ nodes,
+                                                        uint32_t team, uint32_t slots_cap, uint4* __restrict__ nodes,
                                                         uint4* __restrict__ out) {
     const uint32_t lane = threadIdx.x & 31;
     const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -254,7 +267,11 @@ __global__ void __launch_bounds__(128) hash_tree_kernel(const B3Key key, const u
     const uint32_t lt = (uint32_t)(gt % team);
     const uint32_t tmask = (team == 32 ? 0xffffffffu : ((1u << team) - 1u)) << (lane & ~(team - 1));
     uint32_t base = 0, cnt = 0;
-    if (ci < n) { base = P[ci]; cnt = P[ci + 1] - base; }
+    if (ci < n) {
+        base = P[ci];
+        const uint32_t end = ci + 1 < n ? P[ci + 1] : *(P + n + 1);  // P[n + 1]: unclamped total
+        cnt = (end <= slots_cap && end >= base) ? end - base : 0u;    // a chunk that did not fit has no nodes
+    }
     uint4* nd = nodes + 2 * (size_t)base;
     while (cnt > 1) {
         const uint32_t pairs = cnt >> 1;
@@ -287,7 +304,7 @@ HashLayout hash_layout(uint64_t data_bytes, size_t n, int group) {
     L.n_tiles = (n + kTile - 1) / kTile;
     L.slots_cap = (size_t)(data_bytes / ((uint64_t)kLeaf * group)) + n + 1;
     size_t o = 0;
-    L.p_off = o; o = align_up(o + (n + 1) * 4, 256);
+    L.p_off = o; o = align_up(o + (n + 2) * 4, 256);
     L.tiles_off = o; o = align_up(o + (L.n_tiles + 1) * 4, 256);
     L.map_off = o; o = align_up(o + L.slots_cap * 4, 256);
     L.nodes_off = o; o = align_up(o + L.slots_cap * 32, 256);
@@ -324,10 +341,10 @@ cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const u
     uint4* nodes = reinterpret_cast<uint4*>(sb + L.nodes_off);
     int gb = kLeaf * group;
     hash_count_kernel<<<(unsigned)L.n_tiles, kTile, 0, st>>>(off, len, n, gb, P, tiles);
-    hash_tiles_kernel<<<1, 1024, 0, st>>>(tiles, (uint32_t)L.n_tiles, P + n);
-    hash_map_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(off, len, n, gb, P, tiles, map);
-    unsigned blocks = (unsigned)((L.slots_cap + 127) / 128);
+    hash_tiles_kernel<<<1, 1024, 0, st>>>(tiles, (uint32_t)L.n_tiles, (uint32_t)L.slots_cap, P + n);
     uint4* o4 = reinterpret_cast<uint4*>(out);
+    hash_map_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(off, len, n, gb, P, tiles, (uint32_t)L.slots_cap, map, o4);
+    unsigned blocks = (unsigned)((L.slots_cap + 127) / 128);
     static const bool fma_adds = []() { const char* e = getenv("ZEST_B3_PLAIN_ADDS"); return !(e && e[0] == '1'); }();
 #define ZG_LEAF(G)                                                                                                    \
     do {                                                                                                              \
@@ -344,7 +361,7 @@ cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const u
     // team size: a 128 KiB chunk has 128 / G nodes; give each chunk a quarter of that in lanes
     uint32_t team = group == 8 ? 4u : (group == 4 ? 8u : (group == 2 ? 16u : 32u));
     size_t tthreads = n * team;
-    hash_tree_kernel<<<(unsigned)((tthreads + 127) / 128), 128, 0, st>>>(key, P, n, team, nodes, o4);
+    hash_tree_kernel<<<(unsigned)((tthreads + 127) / 128), 128, 0, st>>>(key, P, n, team, (uint32_t)L.slots_cap, nodes, o4);
     return cudaGetLastError();
 }
 
