@@ -210,6 +210,28 @@ ZG_API size_t zg_dev_cdc_scratch_bytes(uint64_t len);
 ZG_API int zg_dev_cdc(zg_ctx* ctx, const uint8_t* d_data, uint64_t len, uint64_t* d_ends, uint64_t cap, uint64_t* d_n_out,
                void* d_scratch, size_t scratch_bytes, void* stream);
 
+/* ---- several GPUs behind one call (SURVEY.md 8b "batch, shards across GPUs", 8e) ------------------------------------ */
+/* zest is one process: XetBridge.reconstructToFile walks a file's terms (src/xet_bridge.zig:231-264) and the parallel
+ * downloader fans them out to one task group (src/parallel_download.zig:91-134, 174-182).  A group gives that one
+ * process every GPU of the box: one context and one worker thread per device.  zg_group_verify_xorbs splits the batch
+ * over the devices by zg_partition_xorbs (greedy longest-first by compressed bytes; xorbs are independent, nothing
+ * moves between GPUs, no collective), every device verifies its part through its own context (own lanes, streams and
+ * PCIe link), and the results come back in the caller's order -- same arguments and same meaning as zg_verify_xorbs.
+ * devices = NULL: devices 0 .. n_devices-1; n_devices <= 0: every visible device.  Pinned buffers from zg_pinned_alloc
+ * of any of the group's contexts are pinned for all of them.  One group call runs at a time; a context obtained with
+ * zg_group_ctx may be used directly (extract, hash, CDC) while no group call is in flight or from other threads. */
+typedef struct zg_group zg_group;
+ZG_API int zg_group_init(const int* devices, int n_devices, const zg_opts* opts, zg_group** out);
+ZG_API void zg_group_shutdown(zg_group* g);
+ZG_API int zg_group_size(const zg_group* g);
+ZG_API zg_ctx* zg_group_ctx(zg_group* g, int i);
+/* part[i] = which of n_parts owns xorb i: longest (by lens[i], the compressed bytes) first, each to the part with the
+ * least bytes so far; ties go to the lower index / lower part, so every caller computes the same split. */
+ZG_API int zg_partition_xorbs(const size_t* lens, size_t n, int n_parts, int32_t* part);
+ZG_API int zg_group_verify_xorbs(zg_group* g, const uint8_t* const* blobs, const size_t* lens, const uint8_t* expected, size_t n,
+                          int8_t* verdict, uint8_t* roots, uint8_t* chunk_hashes, size_t chunk_hash_cap,
+                          uint64_t* bytes_verified);
+
 /* ---- dedup index --------------------------------------------------------------------------- */
 /* A table in HBM from Xet chunk hash to a caller-defined 64-bit location (for instance xorb number << 32 | chunk
  * index).  On the seed/dedup path it answers for a whole batch of hashes what zest asks one file-system probe at a
@@ -243,6 +265,10 @@ ZG_API int zg_dev_int_pipe_peak(void* d_sink, double* alu_gops, double* fma_gops
 /* ---- statistics -------------------------------------------------------------------------------------------- */
 typedef struct zg_stats {
     uint64_t calls, kernels_launched, h2d_bytes, d2h_bytes, bytes_decoded, chunks_hashed;
+    /* GPU time of the stages of zg_verify_xorbs, summed over its sub-batches (CUDA events on each lane's stream;
+     * sub-batches on different lanes overlap, so the sum can exceed the wall time of a call): copies in, LZ4/BG4 decode,
+     * chunk hashing, Merkle fold + compare, results out. */
+    uint64_t ns_h2d, ns_decode, ns_hash, ns_merkle, ns_d2h;
 } zg_stats;
 ZG_API int zg_get_stats(zg_ctx* ctx, zg_stats* out);
 

@@ -365,6 +365,21 @@ static uint32_t xxh32(const uint8_t* p, size_t len, uint32_t seed) {
 }
 OZ_API uint32_t oz_xxh32(const uint8_t* p, size_t len, uint32_t seed) { return xxh32(p, len, seed); }
 
+/* The timed CPU arm may hand independent blocks to liblz4's LZ4_decompress_safe (loaded by lz4_load below) instead of
+ * the plain decoder in this file: zest's CPU path uses an optimised LZ4 decoder too, so this is the fairer number.
+ * Off by default (the oracle proper is the code below); bench.py switches it on and reports which decoder ran.  A
+ * block liblz4 rejects is decoded again by lz4_block, so error codes do not depend on the switch. */
+typedef int (*lz4_decompress_fn)(const char*, char*, int, int);
+static lz4_decompress_fn p_decompress;
+static int g_use_liblz4;
+static pthread_once_t lz4_once = PTHREAD_ONCE_INIT;
+static void lz4_load_once(void);
+OZ_API int oz_set_lz4_decoder(int use_liblz4) {
+    lz4_load_once();
+    g_use_liblz4 = use_liblz4 && p_decompress != NULL;
+    return g_use_liblz4;
+}
+
 /* One LZ4 block: src[0..slen) -> dst[dpos..), matches may reach back to dst[window_lo..).  Returns the
  * new dpos or a negative error.  Byte-serial match copy (overlap semantics of A.4b). */
 static int64_t lz4_block(const uint8_t* src, size_t slen, uint8_t* dst, size_t dpos, size_t dcap,
@@ -453,7 +468,12 @@ static int lz4_frame(const uint8_t* src, size_t slen, uint8_t* dst, size_t ulen)
             dpos += bs;
         } else {
             size_t lo = indep ? dpos : 0; /* linked blocks may reach back (offsets are <= 65535 anyway) */
-            int64_t r = lz4_block(src + ip, bs, dst, dpos, ulen, lo);
+            int64_t r = -1;
+            if (g_use_liblz4 && indep && ulen - dpos <= 0x7E000000u) {
+                int d = p_decompress((const char*)src + ip, (char*)dst + dpos, (int)bs, (int)(ulen - dpos));
+                if (d >= 0) r = (int64_t)dpos + d;
+            }
+            if (r < 0) r = lz4_block(src + ip, bs, dst, dpos, ulen, lo);
             if (r < 0) return (int)r;
             if ((size_t)r - dpos > bmax) return OZ_ERR_LZ4_FRAME;
             dpos = (size_t)r;
@@ -722,7 +742,6 @@ static lz4_bound_fn p_bound;
 static lz4_create_fn p_create;
 static lz4_free_fn p_free;
 static lz4_continue_fn p_continue;
-static pthread_once_t lz4_once = PTHREAD_ONCE_INIT;
 static void lz4_load(void) {
     void* h = dlopen("liblz4.so.1", RTLD_NOW | RTLD_GLOBAL);
     if (!h) return;
@@ -731,7 +750,9 @@ static void lz4_load(void) {
     p_create = (lz4_create_fn)dlsym(h, "LZ4_createStream");
     p_free = (lz4_free_fn)dlsym(h, "LZ4_freeStream");
     p_continue = (lz4_continue_fn)dlsym(h, "LZ4_compress_fast_continue");
+    p_decompress = (lz4_decompress_fn)dlsym(h, "LZ4_decompress_safe");
 }
+static void lz4_load_once(void) { pthread_once(&lz4_once, lz4_load); }
 
 /* Frame `ulen` bytes the way lz4_flex does for xet-core (A.4): FLG 0x60, BD 0x40/0x50, HC, blocks of at most
  * block_max bytes (0 = one block of the frame's maximum), EndMark.  `fflags` exercises the optional parts of the
@@ -821,4 +842,68 @@ OZ_API int64_t oz_build_xorb(const uint8_t* data, const uint64_t* ends, size_t n
     free(grp);
     free(frm);
     return (int64_t)o;
+}
+
+
+/* ------------------------------------------------------------------------------------------------ */
+/* Fast synthetic bf16 bytes for the large bench workloads (input generator only).                  */
+/* ------------------------------------------------------------------------------------------------ */
+
+/* Acklam's rational approximation of the inverse normal CDF (relative error < 1.2e-9). */
+static double inv_norm_cdf(double p) {
+    static const double a[6] = {-3.969683028665376e+01, 2.209460984245205e+02, -2.759285104469687e+02,
+                                1.383577518672690e+02, -3.066479806614716e+01, 2.506628277459239e+00};
+    static const double b[5] = {-5.447609879822406e+01, 1.615858368580409e+02, -1.556989798598866e+02,
+                                6.680131188771972e+01, -1.328068155288572e+01};
+    static const double c[6] = {-7.784894002430293e-03, -3.223964580411365e-01, -2.400758277161838e+00,
+                                -2.549732539343734e+00, 4.374664141464968e+00, 2.938163982698783e+00};
+    static const double d[4] = {7.784695709041462e-03, 3.224671290700398e-01, 2.445134137142996e+00,
+                                3.754408661907416e+00};
+    double q, r;
+    if (p < 0.02425) {
+        q = __builtin_sqrt(-2 * __builtin_log(p));
+        return (((((c[0] * q + c[1]) * q + c[2]) * q + c[3]) * q + c[4]) * q + c[5]) /
+               ((((d[0] * q + d[1]) * q + d[2]) * q + d[3]) * q + 1);
+    }
+    if (p > 1 - 0.02425) return -inv_norm_cdf(1 - p);
+    q = p - 0.5;
+    r = q * q;
+    return (((((a[0] * r + a[1]) * r + a[2]) * r + a[3]) * r + a[4]) * r + a[5]) * q /
+           (((((b[0] * r + b[1]) * r + b[2]) * r + b[3]) * r + b[4]) * r + 1);
+}
+
+static inline uint64_t splitmix64(uint64_t* s) {
+    uint64_t z = (*s += 0x9E3779B97F4A7C15ULL);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+
+/* nbytes of bf16 "weights": float32 sigma * Phi^-1(u), u one of 65,536 equally likely quantiles drawn by a
+ * counter-based generator (splitmix64 keyed by seed), truncated to the top 16 bits.  Same distribution class as
+ * synth_bf16 in xet_oracle.py (float32 N(0, sigma) >> 16; BG4-LZ4 ratio 0.86) at about 1 ns per
+ * value, so that 16 GB - 140 GB sets can be generated in seconds per rank.  Any (seed) stream can be produced by
+ * any thread: the big workloads give every xorb its own seed. */
+OZ_API void oz_synth_bf16_q16(uint8_t* out, size_t nbytes, uint64_t seed, float sigma) {
+    uint16_t* tab = malloc(65536 * sizeof(uint16_t));
+    for (int i = 0; i < 65536; i++) {
+        float v = (float)(sigma * inv_norm_cdf((i + 0.5) / 65536.0));
+        uint32_t bits;
+        memcpy(&bits, &v, 4);
+        tab[i] = (uint16_t)(bits >> 16);
+    }
+    uint64_t st = seed * 0xD1342543DE82EF95ULL + 0x2545F4914F6CDD1DULL;
+    size_t n = nbytes / 2, i = 0;
+    uint16_t* o = (uint16_t*)out; /* callers pass 2-byte aligned buffers (numpy / malloc) */
+    for (; i + 4 <= n; i += 4) {
+        uint64_t r = splitmix64(&st);
+        o[i] = tab[r & 0xffff]; o[i + 1] = tab[(r >> 16) & 0xffff];
+        o[i + 2] = tab[(r >> 32) & 0xffff]; o[i + 3] = tab[r >> 48];
+    }
+    if (i < n || (nbytes & 1)) {
+        uint64_t r = splitmix64(&st);
+        for (; i < n; i++, r >>= 16) o[i] = tab[r & 0xffff];
+        if (nbytes & 1) out[nbytes - 1] = (uint8_t)tab[r & 0xffff];
+    }
+    free(tab);
 }

@@ -72,6 +72,9 @@ def lib():
         L.oz_verify_xorbs_mt.restype = C.c_int64
         L.oz_build_xorb.argtypes = [u8p, u64p, C.c_size_t, C.c_int, C.c_size_t, C.c_int, u8p, C.c_size_t]
         L.oz_build_xorb.restype = C.c_int64
+        L.oz_synth_bf16_q16.argtypes = [u8p, C.c_size_t, C.c_uint64, C.c_float]
+        L.oz_synth_bf16_q16.restype = None
+        L.oz_set_lz4_decoder.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -262,6 +265,22 @@ def build_xorb(data, ends, policy: int, block_max: int = 0, fflags: int = 0) -> 
     return out[:r].tobytes()
 
 
+def build_xorb_into(data, ends, policy: int, out: np.ndarray) -> int:
+    """build_xorb straight into `out` (a uint8 array, e.g. a slice of pinned memory).  -> blob size."""
+    d = _u8(data)
+    e = np.ascontiguousarray(ends, dtype=np.uint64)
+    r = lib().oz_build_xorb(_p(d), _p(e), e.size, policy, 0, 0, out.ctypes.data, out.size)
+    if r < 0:
+        raise OracleError(int(r))
+    return int(r)
+
+
+def set_lz4_decoder(use_liblz4: bool) -> bool:
+    """Timed CPU arm only: hand independent LZ4 blocks to liblz4's LZ4_decompress_safe (True) or keep the plain
+    decoder of xet_oracle.c (False, the default and what the parity tests use).  -> whether liblz4 is in use."""
+    return bool(lib().oz_set_lz4_decoder(1 if use_liblz4 else 0))
+
+
 def split_into_xorbs(ends: np.ndarray):
     """Group consecutive chunks into xorbs of <= 64 MiB and <= 8192 chunks (A.4).  -> list of (lo, hi)."""
     groups, lo, base = [], 0, 0
@@ -333,6 +352,40 @@ def synth_zipf_text(nbytes: int, seed: int) -> np.ndarray:
         out[pos:pos + take] = seg[:take]
         pos += take
     return out[:nbytes]
+
+
+def synth_bf16_fast(nbytes: int, seed: int, sigma: float = 0.02, out: np.ndarray | None = None) -> np.ndarray:
+    """Configs 3-5 at full size: the same kind of bytes as synth_bf16 (Gaussian float32 >> 16) from the oracle's
+    table-driven generator (oz_synth_bf16_q16, ~1 ns per value, GIL released), so that 16-140 GB sets are built in
+    seconds.  Different stream than synth_bf16; BG4-LZ4 ratio 0.862 for both."""
+    if out is None:
+        out = np.empty(nbytes, np.uint8)
+    lib().oz_synth_bf16_q16(out.ctypes.data, nbytes, seed, sigma)
+    return out[:nbytes]
+
+
+def synth_xorb(kind: str, raw_bytes: int, seed: int, policy: int, out: np.ndarray | None = None):
+    """One synthetic xorb from one raw piece (<= 64 MiB): generate, CDC, chunk hashes, Merkle root, serialize.
+    kind: "bf16" | "random" | "text".  -> (blob uint8 array or size written into `out`, expected 32 bytes,
+    chunk_hashes (n,32), ulens u32[n]).  Single-threaded and GIL-free in the heavy parts: run many in a thread pool."""
+    assert raw_bytes <= XORB_MAX_BYTES
+    if kind == "bf16":
+        d = synth_bf16_fast(raw_bytes, seed)
+    elif kind == "random":
+        d = synth_random(raw_bytes, seed)
+    else:
+        d = synth_zipf_text(raw_bytes, seed)
+    ends = cdc(d)
+    assert ends.size <= XORB_MAX_CHUNKS
+    off = np.concatenate([np.zeros(1, np.uint64), ends])
+    hashes = hash_chunks(d, off, 1)
+    lens = np.diff(off)
+    expected = merkle_root(hashes, lens)
+    if out is None:
+        blob = np.frombuffer(build_xorb(d, ends, policy), np.uint8)
+    else:
+        blob = build_xorb_into(d, ends, policy, out)
+    return blob, expected, hashes, lens.astype(np.uint32)
 
 
 def synth_bf16(nbytes: int, seed: int, sigma: float = 0.02) -> np.ndarray:

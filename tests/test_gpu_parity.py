@@ -116,6 +116,38 @@ def test_seal_xorb_reproduces_xet_core_file(ctx, vectors, name):
     assert blob == raw and z.hash_to_hex(root) == rec["xorb_hash"]
 
 
+@pytest.mark.parametrize("name", ["xorb_bf16", "xorb_mixed_auto", "xorb_tiny"])
+def test_sealed_xorb_file_reads_back(ctx, oracle, vectors, name):
+    """Writer and reader round-trip: the stored form (chunk stream + XETBLOB footer, what xet-core's local store and
+    seal_xorb produce) goes straight back through index, verify and extract -- the walk ends where the footer begins."""
+    rec = next(r for r in vectors["real_xorbs"] if r["name"] == name)
+    stream, raw = read_golden_xorb(rec)
+    assert len(raw) > len(stream)
+    ix_s, ix_f = z.xorb_index(stream), z.xorb_index(raw)
+    assert ix_f.n_chunks == ix_s.n_chunks and ix_f.total_ulen == ix_s.total_ulen and np.array_equal(ix_f.hdr_off, ix_s.hdr_off)
+    res = z.verify_xorbs([raw], [z.hex_to_hash(rec["xorb_hash"])], ctx=ctx)
+    assert res.verdict[0] == 1 and res.bytes_verified == rec["n_bytes"]
+    n = ix_s.n_chunks
+    assert z.XorbReader.init(raw, ctx).extractChunkRange(0, n) == oracle.extract_chunk_range(stream, 0, n)
+    # a footer that does not fit its own length word is not a footer: the bytes are walked as chunks and rejected
+    bad = bytearray(raw); bad[-2] ^= 0x40
+    with pytest.raises(z.ZestGpuError):
+        z.xorb_index(bytes(bad))
+
+
+def test_stats_report_gpu_time_per_stage(ctx, oracle):
+    """zg_get_stats: GPU time of the verify stages (copies in, decode, hash, fold, results out) from CUDA events."""
+    data = oracle.synth_zipf_text(3_000_000, 77)
+    xs, _, _ = oracle.make_xorbs(data, 1)
+    s0 = ctx.stats()
+    r = z.verify_xorbs([x.blob for x in xs], [x.expected for x in xs], ctx=ctx)
+    s1 = ctx.stats()
+    assert r.ok
+    for k in ("ns_h2d", "ns_decode", "ns_hash", "ns_merkle", "ns_d2h"):
+        assert s1[k] > s0[k], k
+    assert s1["ns_decode"] - s0["ns_decode"] < 1_000_000_000
+
+
 GENS = {"text": "synth_zipf_text", "bf16": "synth_bf16", "rand": "synth_random"}
 
 

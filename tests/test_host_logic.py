@@ -113,3 +113,22 @@ def test_dedup_shard_of_is_balanced_and_stable():
         counts = np.bincount(s, minlength=n)
         assert counts.min() > 0.9 * h.shape[0] / n
         assert (shard_of(h[::-1], n)[::-1] == s).all()
+
+
+def test_native_partition_matches_the_python_mirror():
+    """zg_partition_xorbs (what zg_group_verify_xorbs splits a batch with) and verify.partition_xorbs (what bench.py
+    splits the global set over ranks with) are the same rule: longest first, least-loaded part, ties to the lower index."""
+    import numpy as np
+    import zest_b200 as z
+    rng = np.random.default_rng(5)
+    for n, parts in [(0, 3), (1, 1), (7, 2), (50, 8), (239, 8), (5, 8), (64, 4)]:
+        sizes = [int(x) for x in rng.integers(1, 1000, n)]
+        tied = list(sizes)
+        if n > 3:
+            tied[1] = tied[2] = tied[0]
+        for s in (sizes, tied, [57_800_000] * n):
+            got = z.partition_native(s, parts)
+            assert got == z.partition_xorbs(s, parts)
+            assert sorted(i for p in got for i in p) == list(range(n))
+            if n >= parts and len(set(s)) == 1:
+                assert max(map(len, got)) - min(map(len, got)) <= 1

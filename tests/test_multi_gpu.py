@@ -73,3 +73,65 @@ def test_sharded_dedup_index_nccl():
                 kept.setdefault(i, set()).add(r)
     assert set(kept) == set(want) and all(v == {want[i] & 0xff} for i, v in kept.items())
     print(f"sharded lookup of 200k hashes per rank: {max(t0, t1):.3f} ms")
+
+
+def _group_case(oz, n_x=9):
+    blobs, expected, gold = [], [], []
+    for i in range(n_x):
+        data = oz.synth_zipf_text(400_000 + 90_000 * i, 40 + i) if i % 3 else oz.synth_bf16(500_000 + 64 * i, 40 + i)
+        xs, _, hs = oz.make_xorbs(data, 1 if i % 3 else 2)
+        blobs.append(xs[0].blob); expected.append(xs[0].expected); gold.append(hs[:xs[0].n_chunks])
+    return blobs, expected, gold
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("devices", [[0], [0, 0], [0, 0, 0], "all"])
+def test_group_verify_matches_oracle_in_caller_order(devices):
+    """One process, several contexts (zg_group): the batch is LPT-partitioned, every part verified through its own
+    context, verdicts / roots / chunk hashes come back in the caller's order and equal the oracle's.  [0, 0] and
+    [0, 0, 0] put two and three contexts on one GPU, so the split-and-reassemble logic is exercised on a one-GPU box
+    too; "all" takes every visible device."""
+    import torch
+    import zest_b200 as z
+    from oracle import xet_oracle as oz
+    blobs, expected, gold = _group_case(oz)
+    bad = bytearray(blobs[4]); bad[len(bad) // 2] ^= 0x21; blobs[4] = bytes(bad)      # payload damage
+    blobs[7] = blobs[7][:len(blobs[7]) - 11]                                          # truncated stream
+    with z.Group(None if devices == "all" else devices) as g:
+        assert g.size == (torch.cuda.device_count() if devices == "all" else len(devices))
+        r = g.verify_xorbs(blobs, expected, want_chunk_hashes=True)
+        r2 = g.verify_xorbs(blobs, expected)                      # without chunk hashes (no counting pass)
+        assert g.context(0).stats()["calls"] > 0
+    v, roots, nb, ch = oz.verify_xorbs(blobs, expected, threads=4, want_chunk_hashes=True)
+    assert np.array_equal(r.verdict, v) and np.array_equal(r2.verdict, v)
+    assert r.verdict[4] != 1 and r.verdict[7] == -3 and (np.delete(r.verdict, [4, 7]) == 1).all()
+    ok = [i for i in range(len(blobs)) if v[i] >= 0]
+    assert np.array_equal(r.roots[ok], roots[ok]) and np.array_equal(r2.roots[ok], roots[ok])
+    want_bytes = sum(int(oz.xorb_index(blobs[i]).total_ulen) for i in range(len(blobs)) if v[i] >= 0)  # xorbs that decoded
+    assert r.bytes_verified == want_bytes == r2.bytes_verified
+    # chunk hashes: back to back in xorb order; the truncated blob (walk error) contributes none
+    pos = 0
+    for i, gh in enumerate(gold):
+        if i == 7:
+            continue
+        k = gh.shape[0]
+        if i != 4:
+            assert np.array_equal(r.chunk_hashes[pos:pos + k], gh), i
+        pos += k
+    assert pos == r.chunk_hashes.shape[0]
+
+
+@pytest.mark.gpu
+def test_group_on_two_gpus_uses_both():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import zest_b200 as z
+    from oracle import xet_oracle as oz
+    blobs, expected, _ = _group_case(oz, 8)
+    with z.Group([0, 1]) as g:
+        r = g.verify_xorbs(blobs, expected)
+        s0, s1 = g.context(0).stats(), g.context(1).stats()
+    assert r.ok and s0["h2d_bytes"] > 0 and s1["h2d_bytes"] > 0
+    parts = z.partition_native([len(b) for b in blobs], 2)
+    assert abs(s0["h2d_bytes"] - sum(len(blobs[i]) for i in parts[0])) < 200_000

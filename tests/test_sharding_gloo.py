@@ -129,3 +129,62 @@ def test_two_rank_sharded_dedup_index():
                 kept.setdefault(i, set()).add(r)
     assert set(kept) == set(want) and all(len(v) == 1 for v in kept.values())
     assert all(((want[i] & 0xff) in v) for i, v in kept.items())
+
+
+def _set_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    import torch
+    import torch.distributed as dist
+    import bench
+    from oracle import xet_oracle as oz
+    from zest_b200 import distributed as zd
+    r, w, _ = zd.init_from_env("gloo")
+    bench.XORB_RAW = 1 << 20          # 1 MiB xorbs so the set is small
+
+    def all_gather_max(a):
+        t = torch.from_numpy(a.copy())
+        if w > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.numpy()
+    xs, n_all, comp_all, part_bytes = bench.build_xorb_set("llama8b-bg4", 7 * (1 << 20) + 12345, 3, r, w, 2,
+                                                           lambda b: np.zeros(b, np.uint8), all_gather_max, lambda m: None)
+    v, roots, nb = oz.verify_xorbs(xs.views, xs.expected, threads=2, want_chunk_hashes=False)[:3]
+    ok = bool((v == 1).all()) and nb == xs.total and np.array_equal(roots, xs.expected)
+    q.put((r, xs.index, xs.sizes, [bytes(b[:64]) + bytes(b[-64:]) for b in xs.views], n_all, comp_all, part_bytes, ok,
+           int(xs.first[-1]), xs.hashes.shape[0], xs.total))
+    zd.shutdown()
+
+
+def test_bench_set_is_one_global_list_partitioned_over_ranks():
+    """bench.build_xorb_set on two gloo ranks against one rank: the same global xorb list (same bytes, whoever built
+    them), split by partition_xorbs on compressed bytes, every rank's part verifies under the oracle."""
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_set_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in ps)
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    q1 = ctx.Queue()
+    p = ctx.Process(target=_set_worker, args=(0, 1, port + 1 if port < 65000 else port - 1, q1))
+    p.start()
+    one = q1.get(timeout=180)
+    p.join(timeout=60)
+    assert p.exitcode == 0 and one[7] and one[1] == list(range(8))
+    (_, i0, s0, e0, n0, c0, pb0, ok0, nc0, nh0, t0), (_, i1, s1, e1, n1, c1, pb1, ok1, nc1, nh1, t1) = res
+    assert ok0 and ok1 and n0 == n1 == 8 and c0 == c1 == one[5] and pb0 == pb1
+    assert sorted(i0 + i1) == list(range(8)) and not set(i0) & set(i1)
+    from zest_b200.verify import partition_xorbs
+    assert [i0, i1] == partition_xorbs(one[2], 2)                      # the split is LPT over the true compressed sizes
+    assert pb0 == [sum(one[2][i] for i in i0), sum(one[2][i] for i in i1)]
+    for idx, sizes, edges in ((i0, s0, e0), (i1, s1, e1)):
+        for i, sz, ed in zip(idx, sizes, edges):
+            assert sz == one[2][i] and ed == one[3][i]                   # same blob whoever built it
+    assert nc0 == nh0 and nc1 == nh1 and t0 + t1 == one[10] == 7 * (1 << 20) + 12345

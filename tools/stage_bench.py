@@ -35,33 +35,20 @@ def main():
     ctx = z.Context(0)
     L = _native.lib()
     t0 = time.time()
-    blobs, expected, gold, total, nchunks = bench.make_workload(args.workload, nbytes, 1, os.cpu_count())
-    print(f"workload {args.workload}: {total/1e6:.0f} MB, {len(blobs)} xorbs, {nchunks} chunks, ratio {sum(map(len, blobs))/total:.3f}, built in {time.time()-t0:.1f}s", flush=True)
-    nx = len(blobs)
-    descs = (ChunkDesc * nchunks)()
-    first = np.zeros(nx + 1, np.uint32)
-    comp = np.zeros(sum(len(b) for b in blobs) + 16 * nx + 64, np.uint8)
-    cpos = dpos = k = 0
-    for i, b in enumerate(blobs):
-        ix = z.xorb_index(b)
-        first[i] = k
-        comp[cpos:cpos + len(b)] = np.frombuffer(b, np.uint8)
-        for j in range(ix.n_chunks):
-            d = descs[k]
-            d.src_off, d.dst_off, d.clen, d.ulen, d.scheme = cpos + int(ix.hdr_off[j]) + 8, dpos, int(ix.clen[j]), int(ix.ulen[j]), int(ix.scheme[j])
-            dpos += (int(ix.ulen[j]) + 15) // 16 * 16
-            k += 1
-        cpos += (len(b) + 15) // 16 * 16
-    first[nx] = k
-    L.zg_chunk_order(C.byref(descs), nchunks)
-    out_bytes = dpos
-    comp_bytes = sum(len(b) for b in blobs)
-    d_comp = torch.from_numpy(comp).to(dev)
-    d_desc = torch.from_numpy(np.frombuffer(descs, np.uint8).copy()).to(dev)
-    d_first = torch.from_numpy(first.view(np.uint8).copy()).to(dev)
-    d_exp = torch.from_numpy(expected.reshape(-1)).to(dev)
-    off = np.array([d.dst_off for d in descs], np.uint64)
-    lens = np.array([d.ulen for d in descs], np.uint32)
+    xs, n_all, comp_bytes, _ = bench.build_xorb_set(args.workload, nbytes, 1, 0, 1, os.cpu_count(), lambda b: np.zeros(b, np.uint8),
+                                                    lambda a: a, lambda m: None)
+    total, gold, expected = xs.total, xs.hashes, xs.expected
+    nx = len(xs.index)
+    descs, out_bytes = bench.build_descs(xs, L)
+    nchunks = descs.size
+    print(f"workload {args.workload}: {total/1e6:.0f} MB, {nx} xorbs, {nchunks} chunks, ratio {comp_bytes/total:.3f}, built in {time.time()-t0:.1f}s", flush=True)
+    cpos = xs.offsets[-1] + (xs.sizes[-1] + 15) // 16 * 16
+    d_comp = torch.from_numpy(xs.buf[:cpos + 64]).to(dev)
+    d_desc = torch.from_numpy(descs.view(np.uint8).reshape(-1)).to(dev)
+    d_first = torch.from_numpy(xs.first.view(np.uint8).copy()).to(dev)
+    d_exp = torch.from_numpy(expected.reshape(-1).copy()).to(dev)
+    off = descs["dst_off"].copy()
+    lens = descs["ulen"].copy()
     d_off, d_len = torch.from_numpy(off.view(np.uint8).copy()).to(dev), torch.from_numpy(lens.view(np.uint8).copy()).to(dev)
     d_out = torch.zeros(out_bytes + 16, dtype=torch.uint8, device=dev)
     d_status = torch.zeros(nchunks, dtype=torch.int32, device=dev)

@@ -28,7 +28,8 @@ SYMBOLS = [
     "zg_dev_verify_scratch_bytes", "zg_dev_verify_xorbs", "zg_dev_cdc_scratch_bytes", "zg_dev_cdc", "zg_get_stats",
     "zg_chunk_order", "zg_dev_hash_chunks_static", "zg_xorb_footer_bytes", "zg_xorb_footer", "zg_dev_int_pipe_peak",
     "zg_dedup_create", "zg_dedup_destroy", "zg_dedup_insert", "zg_dedup_lookup", "zg_dedup_count", "zg_dev_dedup_insert",
-    "zg_dev_dedup_lookup",
+    "zg_dev_dedup_lookup", "zg_group_init", "zg_group_shutdown", "zg_group_size", "zg_group_ctx", "zg_partition_xorbs",
+    "zg_group_verify_xorbs",
 ]
 
 
@@ -47,7 +48,7 @@ class ChunkDesc(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("calls", "kernels_launched", "h2d_bytes", "d2h_bytes", "bytes_decoded",
-                                          "chunks_hashed")]
+                                          "chunks_hashed", "ns_h2d", "ns_decode", "ns_hash", "ns_merkle", "ns_d2h")]
 
 
 def build(verbose: bool = False) -> str:
@@ -119,6 +120,14 @@ def lib() -> C.CDLL:
         L.zg_xorb_footer_bytes.restype = sz
         L.zg_xorb_footer.argtypes = [vp, vp, vp, vp, sz, vp, sz, C.POINTER(sz)]
         L.zg_dev_int_pipe_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), vp]
+        L.zg_group_init.argtypes = [vp, i32, vp, C.POINTER(vp)]
+        L.zg_group_shutdown.argtypes = [vp]
+        L.zg_group_shutdown.restype = None
+        L.zg_group_size.argtypes = [vp]
+        L.zg_group_ctx.argtypes = [vp, i32]
+        L.zg_group_ctx.restype = vp
+        L.zg_partition_xorbs.argtypes = [vp, sz, i32, vp]
+        L.zg_group_verify_xorbs.argtypes = [vp, vp, vp, vp, sz, vp, vp, vp, sz, C.POINTER(u64)]
         L.zg_chunk_order.argtypes = [vp, sz]
         L.zg_chunk_order.restype = None
         _lib = L

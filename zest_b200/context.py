@@ -23,6 +23,14 @@ class Context:
         check(L.zg_init(device, C.byref(o), C.byref(self._h)))
         self.device = device
         self._pinned = {}
+        self._owned = True
+
+    @classmethod
+    def borrowed(cls, handle) -> "Context":
+        """Wrap a context some other object owns (a zg_group's): usable like any other, never shut down from here."""
+        c = cls.__new__(cls)
+        c._h, c.device, c._pinned, c._owned = handle, -1, {}, False
+        return c
 
     @property
     def handle(self):
@@ -34,7 +42,8 @@ class Context:
         if self._h:
             for p in list(self._pinned):
                 self.pinned_free(p)
-            _native.lib().zg_shutdown(self._h)
+            if self._owned:
+                _native.lib().zg_shutdown(self._h)
             self._h = C.c_void_p()
 
     def __enter__(self):

@@ -106,6 +106,7 @@ struct Lane {
     cudaStream_t st = nullptr;
     DevBuf comp, out, meta, res, scratch;  // compressed in, decoded out, descriptors/offsets, results, kernel scratch
     PinBuf hmeta, hres;                    // pinned staging for descriptors and results
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // verify stage marks (created on first use)
     bool busy = false;
 };
 
@@ -117,6 +118,7 @@ struct zg_ctx {
     std::mutex mu;
     std::condition_variable cv;
     std::atomic<uint64_t> calls{0}, kernels{0}, h2d{0}, d2h{0}, decoded{0}, hashed{0};
+    std::atomic<uint64_t> ns_h2d{0}, ns_decode{0}, ns_hash{0}, ns_merkle{0}, ns_d2h{0};  // GPU time per verify stage (events)
 };
 
 namespace {
@@ -152,6 +154,13 @@ int walk(const uint8_t* blob, size_t len, uint32_t stop_after, HostIndex* ix, ui
     size_t pos = 0;
     uint32_t n = 0;
     uint64_t tot = 0;
+    // A stored xorb file (xet-core's local store, zg_xorb_footer / seal_xorb) carries a "XETBLOB" footer after the chunk
+    // stream whose last 4 bytes give its length: the stream ends where that footer begins.
+    if (len >= 100) {
+        const uint8_t* t = blob + len - 4;
+        const uint64_t info = (uint64_t)t[0] | ((uint64_t)t[1] << 8) | ((uint64_t)t[2] << 16) | ((uint64_t)t[3] << 24);
+        if (info + 4 <= len && info >= 92 && memcmp(blob + len - 4 - info, "XETBLOB", 7) == 0) len -= (size_t)info + 4;
+    }
     while (pos < len && n < stop_after) {
         if (len - pos < 8) return fail(ZG_ERR_TRUNCATED, "chunk %u: header runs past the blob", n);
         const uint8_t* h = blob + pos;
@@ -171,12 +180,24 @@ int walk(const uint8_t* blob, size_t len, uint32_t stop_after, HostIndex* ix, ui
     return ZG_OK;
 }
 
-int check_ctx(zg_ctx* ctx) {
-    if (!ctx) return fail(ZG_ERR_INVALID_ARG, "null context");
-    cudaError_t e = cudaSetDevice(ctx->device);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
-    return ZG_OK;
-}
+// Every entry point that takes a context works on that context's device and puts the calling thread's current device
+// back when it returns (a thread with torch on cuda:0 may hold a context on device 1; a zg_group worker and its caller
+// sit on different devices).
+struct DeviceScope {
+    int prev = -1, rc = ZG_OK;
+    explicit DeviceScope(zg_ctx* ctx) {
+        if (!ctx) { rc = fail(ZG_ERR_INVALID_ARG, "null context"); return; }
+        int cur = -1;
+        if (cudaGetDevice(&cur) != cudaSuccess) { (void)cudaGetLastError(); cur = -1; }
+        if (cur == ctx->device) return;
+        cudaError_t e = cudaSetDevice(ctx->device);
+        if (e != cudaSuccess) { rc = cuda_fail(e, "cudaSetDevice"); return; }
+        prev = cur;
+    }
+    ~DeviceScope() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceScope(const DeviceScope&) = delete;
+    DeviceScope& operator=(const DeviceScope&) = delete;
+};
 
 }  // namespace
 
@@ -217,6 +238,7 @@ void zg_shutdown(zg_ctx* c) {
         if (l.st) cudaStreamSynchronize(l.st);
         l.comp.release(); l.out.release(); l.meta.release(); l.res.release(); l.scratch.release();
         l.hmeta.release(); l.hres.release();
+        for (auto& e : l.ev) if (e) cudaEventDestroy(e);
         if (l.st) cudaStreamDestroy(l.st);
     }
     delete c;
@@ -246,14 +268,16 @@ const char* zg_last_error(void) { return g_err; }
 
 int zg_pinned_alloc(zg_ctx* ctx, size_t bytes, void** out) {
     if (!out) return fail(ZG_ERR_INVALID_ARG, "out is null");
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
-    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);  // pinned for every device (zg_group)
     if (e != cudaSuccess) { (void)cudaGetLastError(); *out = nullptr; return fail(ZG_ERR_OOM, "cudaHostAlloc(%zu): %s", bytes, cudaGetErrorString(e)); }
     return ZG_OK;
 }
 int zg_pinned_free(zg_ctx* ctx, void* p) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (p) CU(cudaFreeHost(p));
     return ZG_OK;
@@ -324,7 +348,8 @@ int zg_chunk_range_size(const uint8_t* blob, size_t len, uint32_t start, uint32_
 
 int zg_extract_chunk_range(zg_ctx* ctx, const uint8_t* blob, size_t len, uint32_t start, uint32_t end, uint8_t* out,
                            size_t out_cap, uint64_t* out_len) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if ((!blob && len) || !out_len) return fail(ZG_ERR_INVALID_ARG, "null argument");
     if (start > end) return fail(ZG_ERR_RANGE, "chunk range %u..%u is reversed", start, end);
@@ -385,8 +410,7 @@ namespace {
 
 // One sub-batch of xorbs in flight on a lane.
 struct VerifySlot {
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // ZEST_VERIFY_TRACE: copy start / copy end / kernels end / results on host
-    double t_plan = 0, t_enq = 0;
+    double t_plan = 0, t_enq = 0;  // ZEST_VERIFY_TRACE: host-side times of planning and enqueueing
     Lane* L = nullptr;
     bool launched = false;
     size_t x0 = 0, nx = 0;
@@ -408,7 +432,8 @@ int max_verify_lanes() {  // ZEST_VERIFY_LANES: tuning knob
 int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens, const uint8_t* expected, size_t n,
                     int8_t* verdict, uint8_t* roots, uint8_t* chunk_hashes, size_t chunk_hash_cap,
                     uint64_t* bytes_verified) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (n && (!blobs || !lens || !verdict || !roots)) return fail(ZG_ERR_INVALID_ARG, "null argument");
     if (bytes_verified) *bytes_verified = 0;
@@ -439,12 +464,23 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         if (!S.launched) return ZG_OK;
         S.launched = false;
         CU(cudaStreamSynchronize(S.L->st));
-        if (trace && S.ev[0]) {
-            float a = 0, b = 0, c = 0, d = 0;
-            cudaEventElapsedTime(&a, ev0, S.ev[0]); cudaEventElapsedTime(&b, ev0, S.ev[1]);
-            cudaEventElapsedTime(&c, ev0, S.ev[2]); cudaEventElapsedTime(&d, ev0, S.ev[3]);
-            fprintf(stderr, "[zest trace] xorbs %zu..%zu: planned %.2f enqueued %.2f | copy %.2f-%.2f kernels -%.2f results %.2f | collected %.2f ms\n",
-                    S.x0, S.x0 + S.nx, S.t_plan, S.t_enq, a, b, c, d, now_ms());
+        {   // stage marks of this sub-batch (lane events): GPU time per stage for zg_get_stats, and the trace
+            cudaEvent_t* ev = S.L->ev;
+            float dt[5] = {0, 0, 0, 0, 0};
+            bool okt = ev[5] != nullptr;
+            for (int k = 0; k < 5 && okt; k++) okt = cudaEventElapsedTime(&dt[k], ev[k], ev[k + 1]) == cudaSuccess;
+            if (okt) {
+                ctx->ns_h2d += (uint64_t)(dt[0] * 1e6f); ctx->ns_decode += (uint64_t)(dt[1] * 1e6f); ctx->ns_hash += (uint64_t)(dt[2] * 1e6f);
+                ctx->ns_merkle += (uint64_t)(dt[3] * 1e6f); ctx->ns_d2h += (uint64_t)(dt[4] * 1e6f);
+            } else
+                (void)cudaGetLastError();
+            if (trace && okt) {
+                float a = 0;
+                cudaEventElapsedTime(&a, ev0, ev[0]);
+                fprintf(stderr, "[zest trace] xorbs %zu..%zu: planned %.2f enqueued %.2f | copy %.2f-%.2f decode -%.2f hash -%.2f fold -%.2f results %.2f | collected %.2f ms\n",
+                        S.x0, S.x0 + S.nx, S.t_plan, S.t_enq, a, a + dt[0], a + dt[0] + dt[1], a + dt[0] + dt[1] + dt[2],
+                        a + dt[0] + dt[1] + dt[2] + dt[3], a + dt[0] + dt[1] + dt[2] + dt[3] + dt[4], now_ms());
+            }
         }
         const uint8_t* hr = static_cast<const uint8_t*>(S.L->hres.p);
         memcpy(roots + 32 * S.x0, hr, 32 * S.nx);
@@ -486,10 +522,8 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         if ((rc = collect(S))) break;
         Lane& L = *S.L;
         S.t_plan = t_planned;
-        if (trace) {
-            for (auto& e : S.ev) if (!e) cudaEventCreate(&e);
-            cudaEventRecord(S.ev[0], L.st);
-        }
+        for (auto& e : L.ev) if (!e) cudaEventCreate(&e);
+        cudaEventRecord(L.ev[0], L.st);
         S.x0 = x0; S.nx = nx; S.walk_err = walk_err; S.ulen_total = utot;
         if (chunk_hashes && hashes_written + nc > chunk_hash_cap) {
             rc = fail(ZG_ERR_CAPACITY, "chunk_hashes holds %zu hashes, the batch has more", chunk_hash_cap);
@@ -538,23 +572,26 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         uint8_t* dres = static_cast<uint8_t*>(L.res.p);
         uint8_t* scr = static_cast<uint8_t*>(L.scratch.p);
         if (e == cudaSuccess) e = cudaMemcpyAsync(dm, hm, up_bytes, cudaMemcpyHostToDevice, L.st);
-        if (trace) cudaEventRecord(S.ev[1], L.st);
+        cudaEventRecord(L.ev[1], L.st);
         if (e == cudaSuccess)
             e = launch_decode(static_cast<const uint8_t*>(L.comp.p), cpos, reinterpret_cast<ChunkDesc*>(dm), nc, static_cast<uint8_t*>(L.out.p),
                               ub, reinterpret_cast<int32_t*>(dm + o_status), scr, sz_dec, L.st);
+        cudaEventRecord(L.ev[2], L.st);
         if (e == cudaSuccess)
             e = launch_hash_chunks(static_cast<const uint8_t*>(L.out.p), ub, reinterpret_cast<uint64_t*>(dm + o_off),
                                    reinterpret_cast<uint32_t*>(dm + o_len), nc, make_key(nullptr), dres + r_hashes, scr + sz_dec, sz_hash,
                                    group, L.st);
+        cudaEventRecord(L.ev[3], L.st);
         if (e == cudaSuccess)
             e = launch_merkle(dres + r_hashes, reinterpret_cast<uint32_t*>(dm + o_len), nullptr, reinterpret_cast<uint32_t*>(dm + o_first), nx,
                               nc, reinterpret_cast<int32_t*>(dm + o_status), expected ? dm + o_exp : nullptr, dres,
                               reinterpret_cast<int8_t*>(dres + r_verdict), scr + sz_dec + sz_hash, sz_mer, L.st);
-        if (trace) cudaEventRecord(S.ev[2], L.st);
+        cudaEventRecord(L.ev[4], L.st);
         if (e == cudaSuccess) e = cudaMemcpyAsync(L.hres.p, dres, r_hashes, cudaMemcpyDeviceToHost, L.st);
         if (e == cudaSuccess && chunk_hashes && nc)
             e = cudaMemcpyAsync(chunk_hashes + 32 * hashes_written, dres + r_hashes, 32 * nc, cudaMemcpyDeviceToHost, L.st);
-        if (trace) { cudaEventRecord(S.ev[3], L.st); S.t_enq = now_ms(); }
+        cudaEventRecord(L.ev[5], L.st);
+        if (trace) S.t_enq = now_ms();
         S.launched = true;  // even on a launch error the stream may hold work: collect() drains it
         if (e != cudaSuccess) { rc = cuda_fail(e, "verify pipeline"); break; }
         hashes_written += nc;
@@ -570,8 +607,6 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         if (cr && rc == ZG_OK) rc = cr;
     }
     if (trace) {
-        for (int s = 0; s < n_slots; s++)
-            for (auto& e : slots[s].ev) if (e) cudaEventDestroy(e);
         cudaEventDestroy(ev0);
         fprintf(stderr, "[zest trace] call done %.2f ms\n", now_ms());
     }
@@ -580,7 +615,8 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
 }
 
 int zg_hash_chunks(zg_ctx* ctx, const uint8_t* data, const uint64_t* offsets, size_t n, const uint8_t* key, uint8_t* out) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (n == 0) return ZG_OK;
     if (!offsets || !out) return fail(ZG_ERR_INVALID_ARG, "null argument");
@@ -617,7 +653,8 @@ static const uint8_t kVerificationKey[32] = {127, 24,  87,  214, 206, 86,  237, 
                                              164, 205, 38,  213, 181, 219, 73,  230, 65,  36,  152, 127, 40,  251, 148, 195};
 
 int zg_range_hashes(zg_ctx* ctx, const uint8_t* chunk_hashes, const uint32_t* bounds, size_t n_terms, uint8_t* out) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (n_terms == 0) return ZG_OK;
     if (!chunk_hashes || !bounds || !out) return fail(ZG_ERR_INVALID_ARG, "null argument");
@@ -631,7 +668,8 @@ int zg_range_hashes(zg_ctx* ctx, const uint8_t* chunk_hashes, const uint32_t* bo
 }
 
 int zg_merkle_root(zg_ctx* ctx, const uint8_t* hashes, const uint64_t* lens, size_t n, int file_hash, uint8_t out[32]) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (!out || (n && (!hashes || !lens))) return fail(ZG_ERR_INVALID_ARG, "null argument");
     if (n == 0) { memset(out, 0, 32); return ZG_OK; }
@@ -695,7 +733,8 @@ int cdc_on_lane(zg_ctx* ctx, Lane& L, size_t len, uint64_t* ends, size_t cap, si
 }  // namespace
 
 int zg_cdc(zg_ctx* ctx, const uint8_t* data, size_t len, uint64_t* ends, size_t cap, size_t* n_ends) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (!n_ends || (len && !data)) return fail(ZG_ERR_INVALID_ARG, "null argument");
     *n_ends = 0;
@@ -715,7 +754,8 @@ int zg_cdc(zg_ctx* ctx, const uint8_t* data, size_t len, uint64_t* ends, size_t 
 
 int zg_cdc_hash(zg_ctx* ctx, const uint8_t* data, size_t len, uint64_t* ends, size_t cap, size_t* n_ends, uint8_t* hashes,
                 uint8_t* file_hash) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (!n_ends || (len && !data)) return fail(ZG_ERR_INVALID_ARG, "null argument");
     *n_ends = 0;
@@ -780,7 +820,8 @@ size_t zg_dev_hash_scratch_bytes(uint64_t data_bytes, size_t n) { return hash_sc
 
 int zg_dev_hash_chunks(zg_ctx* ctx, const uint8_t* d_data, uint64_t data_bytes, const uint64_t* d_offsets, const uint32_t* d_lens,
                        size_t n, const uint8_t* key, uint8_t* d_out, void* d_scratch, size_t scratch_bytes, void* stream) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     CU(launch_hash_chunks(d_data, data_bytes, d_offsets, d_lens, n, make_key(key), d_out, d_scratch, scratch_bytes,
                           hash_pick_group(data_bytes), static_cast<cudaStream_t>(stream)));
@@ -793,7 +834,8 @@ size_t zg_dev_decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes) { return
 
 int zg_dev_decode_chunks(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes, const zg_chunk_desc* d_chunks, size_t n_chunks,
                          uint8_t* d_out, uint64_t out_bytes, int32_t* d_status, void* d_scratch, size_t scratch_bytes, void* stream) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     CU(launch_decode(d_comp, comp_bytes, reinterpret_cast<const ChunkDesc*>(d_chunks), n_chunks, d_out, out_bytes, d_status, d_scratch,
                      scratch_bytes, static_cast<cudaStream_t>(stream)));
@@ -807,7 +849,8 @@ size_t zg_dev_merkle_scratch_bytes(size_t n_chunks, size_t n_xorbs) { return mer
 int zg_dev_merkle(zg_ctx* ctx, const uint8_t* d_hashes, const uint32_t* d_lens, const uint32_t* d_first, size_t n_xorbs, size_t n_chunks,
                   const int32_t* d_status, const uint8_t* d_expected, uint8_t* d_roots, int8_t* d_verdict, void* d_scratch,
                   size_t scratch_bytes, void* stream) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     CU(launch_merkle(d_hashes, d_lens, nullptr, d_first, n_xorbs, n_chunks, d_status, d_expected, d_roots, d_verdict, d_scratch,
                      scratch_bytes, static_cast<cudaStream_t>(stream)));
@@ -841,7 +884,8 @@ size_t zg_dev_verify_scratch_bytes(size_t n_chunks, size_t n_xorbs, uint64_t out
 int zg_dev_verify_xorbs(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes, const zg_chunk_desc* d_chunks, size_t n_chunks,
                         const uint32_t* d_first, size_t n_xorbs, const uint8_t* d_expected, uint64_t out_bytes, uint8_t* d_roots,
                         int8_t* d_verdict, uint8_t* d_chunk_hashes, void* d_scratch, size_t scratch_bytes, void* stream) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (n_xorbs == 0) return ZG_OK;
     if (!d_chunk_hashes) return fail(ZG_ERR_INVALID_ARG, "d_chunk_hashes is required (n_chunks x 32 bytes)");
@@ -869,7 +913,8 @@ size_t zg_dev_cdc_scratch_bytes(uint64_t len) { return cdc_scratch_bytes(len); }
 
 int zg_dev_cdc(zg_ctx* ctx, const uint8_t* d_data, uint64_t len, uint64_t* d_ends, uint64_t cap, uint64_t* d_n_out, void* d_scratch,
                size_t scratch_bytes, void* stream) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     CU(launch_cdc(d_data, len, d_ends, cap, d_n_out, d_scratch, scratch_bytes, static_cast<cudaStream_t>(stream)));
     ctx->kernels += 2;
@@ -932,7 +977,8 @@ static int dedup_check_counters(zg_dedup* t, const unsigned long long c[3]) {
 }
 
 int zg_dedup_create(zg_ctx* ctx, size_t max_entries, zg_dedup** out) {
-    int r = check_ctx(ctx);
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (!out || max_entries == 0) return fail(ZG_ERR_INVALID_ARG, "null argument or zero capacity");
     if (max_entries > (1ull << 36)) return fail(ZG_ERR_LIMIT, "dedup index too large");
@@ -954,13 +1000,15 @@ int zg_dedup_create(zg_ctx* ctx, size_t max_entries, zg_dedup** out) {
 
 void zg_dedup_destroy(zg_dedup* t) {
     if (!t) return;
+    DeviceScope dev_scope(t->ctx);
     if (t->mem) cudaFree(t->mem);
     delete t;
 }
 
 int zg_dedup_insert(zg_dedup* t, const uint8_t* hashes, const uint64_t* locations, size_t n, uint8_t* was_new) {
     if (!t) return fail(ZG_ERR_INVALID_ARG, "null table");
-    int r = check_ctx(t->ctx);
+    DeviceScope dev_scope(t->ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (n == 0) return ZG_OK;
     if (!hashes || !locations) return fail(ZG_ERR_INVALID_ARG, "null argument");
@@ -990,7 +1038,8 @@ int zg_dedup_insert(zg_dedup* t, const uint8_t* hashes, const uint64_t* location
 
 int zg_dedup_lookup(zg_dedup* t, const uint8_t* hashes, size_t n, uint64_t* locations) {
     if (!t) return fail(ZG_ERR_INVALID_ARG, "null table");
-    int r = check_ctx(t->ctx);
+    DeviceScope dev_scope(t->ctx);
+    int r = dev_scope.rc;
     if (r) return r;
     if (n == 0) return ZG_OK;
     if (!hashes || !locations) return fail(ZG_ERR_INVALID_ARG, "null argument");
@@ -1012,15 +1061,22 @@ int zg_dedup_lookup(zg_dedup* t, const uint8_t* hashes, size_t n, uint64_t* loca
 
 int zg_dedup_count(zg_dedup* t, uint64_t* entries) {
     if (!t || !entries) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    DeviceScope dev_scope(t->ctx);
+    if (dev_scope.rc) return dev_scope.rc;
     std::lock_guard<std::mutex> lk(t->mu);
     unsigned long long c[3];
-    CU(cudaMemcpy(c, t->v.counters, 24, cudaMemcpyDeviceToHost));  // waits for all earlier work on the device
+    // The inserts whose errors surface here may sit on any stream (the library's lanes and torch's streams are
+    // non-blocking ones, which a copy on the legacy default stream does not wait for): drain the whole device first.
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(c, t->v.counters, 24, cudaMemcpyDeviceToHost));
     *entries = c[0];
     return dedup_check_counters(t, c);
 }
 
 int zg_dev_dedup_insert(zg_dedup* t, const uint8_t* d_hashes, const uint64_t* d_locations, size_t n, uint8_t* d_was_new, void* stream) {
     if (!t) return fail(ZG_ERR_INVALID_ARG, "null table");
+    DeviceScope dev_scope(t->ctx);
+    if (dev_scope.rc) return dev_scope.rc;
     if (n == 0) return ZG_OK;
     if (!d_hashes || !d_locations) return fail(ZG_ERR_INVALID_ARG, "null argument");
     CU(launch_dedup_insert(t->v, d_hashes, d_locations, n, ++t->epoch, d_was_new, static_cast<cudaStream_t>(stream)));
@@ -1030,6 +1086,8 @@ int zg_dev_dedup_insert(zg_dedup* t, const uint8_t* d_hashes, const uint64_t* d_
 
 int zg_dev_dedup_lookup(zg_dedup* t, const uint8_t* d_hashes, size_t n, uint64_t* d_locations, void* stream) {
     if (!t) return fail(ZG_ERR_INVALID_ARG, "null table");
+    DeviceScope dev_scope(t->ctx);
+    if (dev_scope.rc) return dev_scope.rc;
     if (n == 0) return ZG_OK;
     if (!d_hashes || !d_locations) return fail(ZG_ERR_INVALID_ARG, "null argument");
     CU(launch_dedup_lookup(t->v, d_hashes, n, d_locations, static_cast<cudaStream_t>(stream)));
@@ -1041,6 +1099,8 @@ int zg_get_stats(zg_ctx* ctx, zg_stats* out) {
     if (!ctx || !out) return fail(ZG_ERR_INVALID_ARG, "null argument");
     out->calls = ctx->calls; out->kernels_launched = ctx->kernels; out->h2d_bytes = ctx->h2d; out->d2h_bytes = ctx->d2h;
     out->bytes_decoded = ctx->decoded; out->chunks_hashed = ctx->hashed;
+    out->ns_h2d = ctx->ns_h2d; out->ns_decode = ctx->ns_decode; out->ns_hash = ctx->ns_hash; out->ns_merkle = ctx->ns_merkle;
+    out->ns_d2h = ctx->ns_d2h;
     return ZG_OK;
 }
 

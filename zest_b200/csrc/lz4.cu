@@ -8,35 +8,41 @@
 //
 // Mapping.  One warp decodes one chunk at a time (chunks are handed out longest-first through a ticket counter,
 // 24 single-warp CTAs per SM).  LZ4's token stream is serial, and on real Xet data the sequences are tiny (text:
-// ~5,900 per 64 KiB chunk, ~11 output bytes each), so a lane-serial walk leaves 31 lanes idle and costs ~100 warp
-// instructions per sequence.  The walk is therefore SPECULATIVE and warp-wide, in rounds:
-//   parse   : the next 32 x 68 stream bytes of the block are staged in shared memory (cp.async) and cut into 32
-//             segments; lane k walks tokens from the first byte of segment k as if a sequence started there.  Lane 0
-//             starts at the true position.  A chain that starts on a wrong byte falls onto true sequence boundaries
-//             after a few hops (each hop lands on one with probability ~1/sequence length, and once on one it stays
-//             on them; measured on text: median 29 bytes, 95 % within 155), so after its own segment every lane
-//             walks on into the following ones until it reaches a position that segment's own chain visited -- the
-//             JOIN.  Visited positions are one bit each in a shared bit map; records (position, literal length,
-//             match length, offset; 8 bytes) go to a pool whose slots are handed out per iteration by ballot.
-//   resolve : lane 0 is true; a lane is true from its join position on iff the chain before it is true and joined
-//             it (pointer doubling over the join links, 5 shuffle rounds).  True records are numbered in stream
-//             order by a warp scan.  A chain that meets anything unusual (end of block, oversized length, zero
-//             offset, pool full) simply stops; if it was the true chain, the serial walker takes over at that byte.
-//   execute : 32 consecutive true sequences per step, one per lane: output positions by a warp scan of the lengths,
-//             the offset/size checks of the oracle on those positions, then literals and matches whose source
-//             precedes the step in one pass (all loads before all stores), and the matches that read the step's
-//             own output in rounds, each as soon as the matches it reads from are done (dependency masks by
-//             binary search over the lanes).  Runs longer than 16 bytes are copied by the whole warp.
-//   serial  : frame and block headers, the last sequence of a block, stored blocks, oversized pieces and every error
-//             go through a plain one-sequence-at-a-time walker that mirrors the oracle check for check; it runs
-//             uniformly on all lanes (same instructions, no broadcasts) and feeds the same execute step.
-// Output goes to global memory (a 64 MiB xorb stays resident in the 126 MB L2); byte-group regrouping is done by
-// the warp when a scheme-2 chunk completes, reading the planes back from L2.
+// ~5,900 per 64 KiB chunk, ~11 output bytes each; the exponent planes of bf16 tensors: ~14 bytes each), so a lane-serial
+// walk leaves 31 lanes idle and costs ~100 warp instructions per sequence.  The walk is therefore done for EVERY byte
+// position at once, in rounds over the next 32 x 68 stream bytes of the block:
+//   tables  : the bytes are staged in shared memory (cp.async); lane k takes the 68 positions of segment k and works out,
+//             for each of them, how long a sequence starting there would be (token, at most one length byte each,
+//             literals, offset) -- the HOP table, one byte per position, 0 where no such sequence fits -- and, walking
+//             its segment backwards, where the chain of hops from each position leaves the segment -- the EXIT table.
+//             The same ~40 instructions per position on every lane, whatever the data; nothing speculative, nothing
+//             thrown away, no dependent chain longer than two shared-memory reads.
+//   compose : the true chain enters segment 0 at the known position; one exit-table look-up per segment carries it
+//             across the round (32 dependent shared-memory reads, uniform across the warp), which gives every lane the
+//             position at which the true chain enters its segment.
+//   list    : each lane follows the hop table from that entry to the end of its segment (<= 23 hops), counting and
+//             noting the token positions; a warp scan orders them, and the positions go to a list in stream order.
+//   execute : 32 consecutive true sequences per step, one per lane, re-read from the staged bytes: output positions by
+//             a warp scan of the lengths, the offset/size checks of the oracle on those positions, then literals (from
+//             the staged window) and matches whose source precedes the step in one pass (all loads before all stores),
+//             and the matches that read the step's own output in rounds, each as soon as the matches it reads from are
+//             done (dependency masks by binary search over the lanes).  Runs longer than 16 bytes are copied by the
+//             whole warp.
+//   serial  : frame and block headers, the last sequence of a block, stored blocks, sequences longer than 255 stream
+//             bytes (long literal runs -- the mantissa planes of byte-grouped bf16 are one 16 KiB run each -- and
+//             matches of more than 273 bytes) and every error go through a plain one-sequence-at-a-time walker that
+//             mirrors the oracle check for check; it runs uniformly on all lanes (same instructions, no broadcasts) and
+//             feeds the same execute step.  A table round that stops early hands over to it; if rounds keep stopping
+//             early (runs of zeros: every sequence is long) the walker's turns get longer.
+// Round 1 walked the stream speculatively instead (lane k parsed from the first byte of segment k and chains were
+// joined where they met): on bf16 planes 2.8 sequences were parsed for every true one and parse + join were 51 % of
+// all instructions (profiles/r2_ncu_decode_bf16_baseline_by_region.txt); the tables cost the same on any data.
+// Output goes to global memory; byte-group regrouping is done by the warp when a scheme-2 chunk completes, reading
+// the planes back from L2.
 //
 // Roofline: HBM-bound in principle (compressed bytes in + decoded bytes out).  In practice the kernel is bound by
-// instruction issue: ~36 warp instructions per sequence (profiles/r1_ncu_decode_spec*.txt), 55 % of the issue
-// slots busy with 24 warps per SM, the rest lost to dependent-instruction and memory latency inside each chunk's
-// chain.  bench.py reports achieved GB/s over the algorithmic bytes.
+// instruction issue and by the latency of each chunk's chain; bench.py reports achieved GB/s over the algorithmic
+// bytes, profiles/ holds the ncu summaries.
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -58,38 +64,24 @@ constexpr uint32_t kMaxPiece = 65535;
 #endif
 constexpr int kNP = ZG_NP;            // groups of 32 sequences per execute step
 constexpr uint32_t kSerialCap = 16;   // sequences per round of the serial walker
-#ifndef ZG_SEG
-#define ZG_SEG 68
-#endif
-#ifndef ZG_JOIN
-#define ZG_JOIN 64
-#endif
-constexpr uint32_t kSeg = ZG_SEG;       // speculative segment, stream bytes: 17 words, so 32 lanes start in 32 banks
-constexpr uint32_t kCap = 24;         // a 68-byte segment holds at most 23 sequences
-constexpr uint32_t kJoinHops = ZG_JOIN;    // sequences a chain may walk beyond its segment looking for its join
-#ifndef ZG_POOL
-#define ZG_POOL 512
-#endif
-constexpr uint32_t kPool = ZG_POOL;       // records per round, all lanes together (slots are handed out per iteration)
-#ifndef ZG_PREROLL
-#define ZG_PREROLL 32     // run-up bytes in front of each speculative segment (0: none)
-#endif
-constexpr uint32_t kSpanMax = 32 * kSeg;
-constexpr uint32_t kWinBytes = 2304;  // staged stream bytes: alignment slack + span + >= 100 bytes beyond it
-constexpr int32_t kNotTrue = INT32_MIN;
-constexpr uint32_t kSpecMin = 32;     // blocks (or block remainders) shorter than this go to the serial walker
+constexpr uint32_t kSeg = 68;          // stream bytes per lane and round: 17 words, so 32 lanes start in 32 banks
+constexpr uint32_t kSpan = 32 * kSeg;  // stream bytes parsed per round
+constexpr uint32_t kHopMax = 255;      // longest sequence (token .. last length byte) the table holds; longer ones go serial
+constexpr uint32_t kWinBytes = 2432;   // staged stream bytes: the span + the longest hop, rounded up to 16
+constexpr uint32_t kSlots = 26;        // list slots per lane (a 68-byte segment holds at most 23 sequences); 13 words: no bank conflicts
+constexpr uint32_t kStop = 255;        // exit-table mark: the chain from here ends inside the segment
+constexpr uint32_t kNone = 0xffffffffu;
+constexpr uint32_t kSpecMin = 32;      // blocks (or block remainders) shorter than this go to the serial walker
 
 enum : int { ST_IDLE = 0, ST_START, ST_BLOCK_HDR, ST_IN_BLOCK, ST_AFTER_BLOCK, ST_FINISH, ST_EXHAUSTED };
 
 struct WarpShared {
-    uint4 win[kWinBytes / 16];       // staged stream window; after the walk: true records in stream order (pool slots)
-    uint32_t bmp[kSpanMax / 32];     // bit map over the span: positions visited by the chain of the segment they lie in
-    uint2 pool[kPool];               // records of the round: {pos - ip | lit << 16, ml | off << 16}
-    uint16_t meta[kPool];            // per record: lane << 8 | number of the record within its lane's chain
-    uint32_t sj[32];                 // per lane: number of its first true record, posted by the chain that joins it
-    uint32_t first[32];              // per lane: the same, for everyone to read
-    int32_t base[32];                // per lane: stream-order index of its record number 0 (kNotTrue: lane not true)
-    uint32_t srec[kSerialCap * 3];   // serial walker records: literal source, lit | ml << 16, offset
+    uint4 win[kWinBytes / 16];   // staged stream window (window byte w = stream byte ip - a0 + w, a0 = alignment of ip)
+    uint8_t nxt[kSpan];          // per window byte: stream length of the sequence whose token sits there (0: none);
+                                 // after the chain walk: the true token positions in stream order (u16 each)
+    uint8_t ex[kSpan];           // per window byte: where the chain from there leaves its lane's segment, relative to the
+                                 // segment end (kStop: it ends inside); after compose: per-lane position slots (u16)
+    uint32_t srec[kSerialCap * 3];  // serial walker records: literal source, lit | ml << 16, offset
 };
 
 __device__ __forceinline__ uint32_t rd8(const uint8_t* p) { return __ldg(p); }
@@ -141,6 +133,23 @@ __device__ __forceinline__ void load16(const uint8_t* s, uint32_t n, uint32_t (&
     uint32_t v[5];
     v[0] = ld_word_if<READ_ONLY, 0>(w, span); v[1] = ld_word_if<READ_ONLY, 1>(w, span); v[2] = ld_word_if<READ_ONLY, 2>(w, span);
     v[3] = ld_word_if<READ_ONLY, 3>(w, span); v[4] = ld_word_if<READ_ONLY, 4>(w, span);
+#pragma unroll
+    for (int k = 0; k < 4; k++) x[k] = __funnelshift_r(v[k], v[k + 1], sh);
+}
+// The same from the staged stream window in shared memory (literal runs of a table round).
+template <int K>
+__device__ __forceinline__ uint32_t lds_word_if(uint32_t w, uint32_t span) {
+    uint32_t v;
+    asm volatile("{ .reg .pred p; setp.gt.u32 p, %1, %2; mov.u32 %0, 0; @p ld.shared.u32 %0, [%3+%2]; }"
+                 : "=r"(v) : "r"(span), "n"(4 * K), "r"(w) : "memory");
+    return v;
+}
+__device__ __forceinline__ void load16_win(const uint8_t* s, uint32_t n, uint32_t (&x)[4]) {
+    const uint32_t a = (uint32_t)__cvta_generic_to_shared(s);
+    const uint32_t w = a & ~3u, sh = (a & 3u) * 8, span = n ? (a & 3u) + n : 0;
+    uint32_t v[5];
+    v[0] = lds_word_if<0>(w, span); v[1] = lds_word_if<1>(w, span); v[2] = lds_word_if<2>(w, span);
+    v[3] = lds_word_if<3>(w, span); v[4] = lds_word_if<4>(w, span);
 #pragma unroll
     for (int k = 0; k < 4; k++) x[k] = __funnelshift_r(v[k], v[k + 1], sh);
 }
@@ -259,101 +268,69 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // Stage kWinBytes of the stream starting at the 16-byte-aligned address A (clipped at the padded end of the
-// compressed buffer) and clear the position map.  Asynchronous: wait + __syncwarp before use.
+// compressed buffer; what is not staged keeps stale bytes, which lie beyond every block end).  Asynchronous: wait +
+// __syncwarp before use.
 __device__ __forceinline__ void stage_window(WarpShared& ws, uintptr_t A, const uint8_t* comp_hi, uint32_t lane) {
     const uint8_t* g = reinterpret_cast<const uint8_t*>(A);
 #pragma unroll
     for (uint32_t i = lane; i < kWinBytes / 16; i += 32)
         if (g + 16 * i + 16 <= comp_hi) cp_async16(&ws.win[i], g + 16 * i);
+}
+
+// Hop table + exit table of one lane's segment, window bytes [seg0, seg0 + kSeg), highest position first.
+//   nxt[w] = length in the stream of the sequence whose token is at w, had a sequence started there: token, at most one
+//            literal-length byte, the literals, the offset, at most one match-length byte.  0 when that is not a
+//            sequence the round can take: it would end past the block (which covers the block's last, literals-only
+//            sequence), its offset is 0, a length needs more than one extra byte, or it is longer than kHopMax.  Purely
+//            positional: the checks that need the output position are made at execute time.
+//   ex[w]  = where the chain of hops from w first leaves the segment, relative to the segment end (< kHopMax), or kStop
+//            if it runs into a 0 before that.  One look-up per segment then carries the true chain across the round.
+// Every position costs the same ~40 instructions on every lane, whatever the data: no speculation, nothing discarded.
+__device__ __forceinline__ void build_tables(WarpShared& ws, uint32_t seg0, uint32_t bend_w) {
+    const uint8_t* const win = reinterpret_cast<const uint8_t*>(ws.win);
+    const uint32_t* const ww = reinterpret_cast<const uint32_t*>(ws.win) + seg0 / 4;
+    const uint32_t segend = seg0 + kSeg;
+    uint32_t hi = ww[kSeg / 4];
 #pragma unroll
-    for (uint32_t i = lane; i < kSpanMax / 32; i += 32) ws.bmp[i] = 0;
-}
-
-// One speculative hop: the sequence whose token sits at stream position pos (relative to the chunk payload).
-// Positional checks only; anything unusual makes the chain stop in front of this sequence (ok = false).
-// wofs = window offset of stream position 0 (may wrap), so position p sits at window byte p + wofs.
-struct Hop {
-    uint32_t lit, ml, off, nip;
-    bool ok;
-};
-__device__ __forceinline__ uint32_t stream_byte(const uint8_t* src, const uint8_t* win, uint32_t wofs, uint32_t p) {
-    const uint32_t r = p + wofs;
-    return r < kWinBytes ? (uint32_t)win[r] : rd8(src + p);
-}
-__device__ __noinline__ Hop spec_hop_general(const uint8_t* src, const uint8_t* win, uint32_t wofs, uint32_t pos, uint32_t bend);
-
-// The common case without a branch: at most one extension byte per length, everything inside the staged window.
-// Two dependent shared-memory reads: token + first literal-length byte, then offset + first match-length byte.
-__device__ __forceinline__ Hop spec_hop(const uint8_t* src, const uint8_t* win, uint32_t wofs, uint32_t pos, uint32_t bend) {
-    const uint32_t r = pos + wofs;
-    if (r <= kWinBytes - 8) {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(win + (r & ~3u));
-        const uint32_t t = __funnelshift_r(w[0], w[1], (r & 3u) * 8);
-        const uint32_t tok = t & 0xffu, e1 = (t >> 8) & 0xffu;
-        const uint32_t lit4 = tok >> 4, ml4 = tok & 15u;
-        const bool lx = lit4 == 15u, mx = ml4 == 15u;
-        const uint32_t lit = lit4 + (lx ? e1 : 0u);
-        const uint32_t o = 1u + (lx ? 1u : 0u) + lit;  // the offset's distance from the token
-        const uint32_t r2 = r + o;
-        if (r2 <= kWinBytes - 8) {
-            const uint32_t* v = reinterpret_cast<const uint32_t*>(win + (r2 & ~3u));
-            const uint32_t u = __funnelshift_r(v[0], v[1], (r2 & 3u) * 8);
-            const uint32_t e2 = (u >> 16) & 0xffu;
-            if (!((lx && e1 == 255u) || (mx && e2 == 255u))) {
-                Hop h;
-                h.lit = lit; h.off = u & 0xffffu; h.ml = ml4 + 4u + (mx ? e2 : 0u);
-                h.nip = pos + o + 2u + (mx ? 1u : 0u);
-                h.ok = h.nip <= bend && h.off != 0;  // offset (and extension byte) inside the block
-                return h;
-            }
+    for (int i = kSeg / 4 - 1; i >= 0; i--) {
+        const uint32_t cur = ww[i];
+        uint32_t packed = 0;
+#pragma unroll
+        for (int j = 3; j >= 0; j--) {
+            const uint32_t w = seg0 + 4 * i + j;
+            const uint32_t b0 = (cur >> (8 * j)) & 0xffu;
+            const uint32_t b1 = j < 3 ? (cur >> (8 * j + 8)) & 0xffu : hi & 0xffu;
+            const uint32_t lit4 = b0 >> 4;
+            const uint32_t adv = lit4 == 15u ? b1 + 16u : lit4;  // literal bytes + the length byte, if any
+            const uint32_t o = w + 1u + adv;                      // where the offset sits
+            const uint8_t* q = win + min(o, w + (kHopMax - 2u));   // clamped: anything further is too long anyway
+            const uint32_t off = (uint32_t)q[0] | ((uint32_t)q[1] << 8), e2 = q[2];
+            const bool mx = (b0 & 15u) == 15u;
+            const uint32_t nip = o + 2u + (mx ? 1u : 0u);
+            const uint32_t d = nip - w;
+            const bool ok = off != 0u && !(mx && e2 == 255u) && nip <= bend_w && d <= kHopMax;
+            const uint32_t dd = ok ? d : 0u;
+            packed |= dd << (8 * j);
+            // exit of the chain from w: through nip if that is still inside the segment
+            const uint32_t inside = ws.ex[min(nip, segend - 1u)];
+            const uint32_t x = !ok ? kStop : (nip >= segend ? nip - segend : inside);
+            ws.ex[w] = (uint8_t)x;
         }
+        reinterpret_cast<uint32_t*>(ws.nxt)[seg0 / 4 + i] = packed;
+        hi = cur;
     }
-    return spec_hop_general(src, win, wofs, pos, bend);
 }
 
-__device__ __noinline__ Hop spec_hop_general(const uint8_t* src, const uint8_t* win, uint32_t wofs, uint32_t pos, uint32_t bend) {
-    Hop h;
-    h.ok = false; h.lit = h.ml = h.off = 0; h.nip = pos;
-    const uint32_t r = pos + wofs;
-    uint64_t w64;
-    if (r <= kWinBytes - 12) {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(win + (r & ~3u));
-        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], sh = (r & 3u) * 8;
-        w64 = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
-    } else
-        w64 = load_window(src + pos);
-    const uint32_t tok = (uint32_t)w64 & 0xffu;
-    uint32_t lit = tok >> 4, ml = tok & 15u, q = pos + 1;
-    if (lit == 15u) {
-        uint32_t b;
-        do {
-            if (q >= bend) return h;
-            b = (q - pos < 8) ? (uint32_t)(w64 >> (8 * (q - pos))) & 0xffu : stream_byte(src, win, wofs, q);
-            q++;
-            lit += b;
-            if (lit > kMaxPiece) return h;
-        } while (b == 255u);
-    }
-    const uint32_t o = q + lit;  // position of the offset
-    if (o + 2 > bend) return h;  // includes the literals-only last sequence of a block
-    uint32_t off;
-    if (o - pos <= 6) off = (uint32_t)(w64 >> (8 * (o - pos))) & 0xffffu;
-    else off = stream_byte(src, win, wofs, o) | (stream_byte(src, win, wofs, o + 1) << 8);
-    q = o + 2;
-    if (ml == 15u) {
-        uint32_t b;
-        do {
-            if (q >= bend) return h;
-            b = (q - pos < 8) ? (uint32_t)(w64 >> (8 * (q - pos))) & 0xffu : stream_byte(src, win, wofs, q);
-            q++;
-            ml += b;
-            if (ml > kMaxPiece - 4) return h;
-        } while (b == 255u);
-    }
-    ml += 4;
-    if (off == 0) return h;
-    h.lit = lit; h.ml = ml; h.off = off; h.nip = q; h.ok = true;
-    return h;
+// The sequence at window byte w, in full (execute step; w is a true token position, so it is one the table accepted).
+__device__ __forceinline__ void seq_at(const uint8_t* win, uint32_t w, uint32_t& lit, uint32_t& ml, uint32_t& off, uint32_t& lit_w) {
+    const uint32_t b0 = win[w], b1 = win[w + 1];
+    const uint32_t lit4 = b0 >> 4;
+    const bool lx = lit4 == 15u, mx = (b0 & 15u) == 15u;
+    lit = lit4 + (lx ? b1 : 0u);
+    lit_w = w + 1u + (lx ? 1u : 0u);
+    const uint8_t* q = win + lit_w + lit;
+    off = (uint32_t)q[0] | ((uint32_t)q[1] << 8);
+    ml = (b0 & 15u) + 4u + (mx ? (uint32_t)q[2] : 0u);
 }
 
 // The matches of up to 32 sequences in stream order, one per lane (ml = 0: none), whose sources may lie in the
@@ -408,10 +385,10 @@ __device__ __forceinline__ void match_rounds(uint8_t* lz, uint32_t md, uint32_t 
 // step's first byte; everything below op0 is final.  Pass 1 copies every literal run and every match whose source
 // lies wholly below op0 (most of them) with all loads of the step in flight together; the matches that read the
 // step's own output follow in match_rounds.
-template <int NP>
-__device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint32_t op0, const uint32_t (&lit_src)[NP],
-                                           const uint32_t (&lit)[NP], uint32_t (&ml)[NP], const uint32_t (&off)[NP],
-                                           const uint32_t (&dst)[NP], uint32_t lane) {
+template <int NP, bool LIT_WIN>
+__device__ __forceinline__ void exec_group(const uint8_t* src, const uint8_t* win, uint8_t* lz, uint32_t op0, const uint32_t (&lit_src)[NP],
+                                           const uint32_t (&lit_w)[NP], const uint32_t (&lit)[NP], uint32_t (&ml)[NP],
+                                           const uint32_t (&off)[NP], const uint32_t (&dst)[NP], uint32_t lane) {
     __syncwarp();
 #ifdef ZG_LZ4_PROFILE
     const long long pt0 = clock64();
@@ -426,7 +403,10 @@ __device__ __forceinline__ void exec_group(const uint8_t* src, uint8_t* lz, uint
         k[q] = (old[q] && ml[q] <= kShort) ? ml[q] : 0u;
     }
 #pragma unroll
-    for (int q = 0; q < NP; q++) load16<true>(src + lit_src[q], n[q], x[q]);
+    for (int q = 0; q < NP; q++) {
+        if (LIT_WIN) load16_win(win + lit_w[q], n[q], x[q]);  // short literal runs of a table round sit in the staged window
+        else load16<true>(src + lit_src[q], n[q], x[q]);
+    }
 #pragma unroll
     for (int q = 0; q < NP; q++) load16<false>(lz + dst[q] + lit[q] - off[q], k[q], y[q]);
 #pragma unroll
@@ -487,8 +467,9 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
     __shared__ __align__(16) WarpShared ws;
     const uint32_t lane = threadIdx.x;
     const uint8_t* const win = reinterpret_cast<const uint8_t*>(ws.win);
-    uint16_t* const ref = reinterpret_cast<uint16_t*>(ws.win);  // the window is dead once the walk is over
-    static_assert(kPool * 2 <= kWinBytes, "stream-order list must fit the window");
+    uint16_t* const slots = reinterpret_cast<uint16_t*>(ws.ex);   // per-lane token positions (the exit table is dead by then)
+    uint16_t* const list = reinterpret_cast<uint16_t*>(ws.nxt);   // true token positions in stream order (the hop table is dead by then)
+    static_assert(32 * kSlots * 2 <= kSpan && (kSpan / 3 + 1) * 2 <= kSpan, "slots and list must fit the tables they alias");
 
     // Chunk state.  Warp-uniform: every lane holds the same values and the serial walker runs identically on all
     // lanes (same cost as running it on one, and nothing has to be broadcast).
@@ -500,8 +481,8 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
     uint32_t ip = 0, bend = 0, op = 0, win_lo = 0, blk_op = 0, bmax = 0, fflags = 0;  // fflags: 1 indep, 2 bsum, 4 csum
     uint32_t p_lit = 0, p_lsrc = 0, p_mlen = 0, p_off = 0;
     int err = 0;
-    bool force_serial = false;  // the last speculative round made no progress: one serial round first
-    uint32_t seglim = 32;       // segments per speculative round (fewer where sequences are dense: the record pool is finite)
+    uint32_t serial_rounds = 0;  // serial rounds to run before the next table round (the last one stopped early)
+    uint32_t backoff = 1;        // ... and how many next time, should that one stop early too
 
 #ifdef ZG_LZ4_PROFILE
     long long t_parse = 0, t_res = 0, t_exec = 0, t_serial = 0, n_spec = 0, n_serial = 0, n_true = 0, n_parsed = 0, tq;
@@ -526,171 +507,86 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
             fin_out = out + d.dst_off;
             lz = scheme == 2 ? tmp + d.dst_off : fin_out;
             ip = 0; op = 0; err = 0; p_lit = p_mlen = 0;
-            force_serial = false;
-            seglim = 32;
+            serial_rounds = 0; backoff = 1;
             state = ST_START;
         }
 
-        if (state == ST_IN_BLOCK && (p_lit | p_mlen) == 0 && !force_serial && bend - ip >= kSpecMin) {
-            // ================= speculative round =================
-            const uint32_t nseg = min(seglim, (bend - ip + kSeg - 1) / kSeg);  // the last segment may be short
-            const uint32_t spanend = min(ip + nseg * kSeg, bend);
-            const uintptr_t a0 = reinterpret_cast<uintptr_t>(src) + ip;
-            const uintptr_t wbase = a0 & ~(uintptr_t)15;
-            __syncwarp();  // the previous round's stream-order list lives in the window
+        if (state == ST_IN_BLOCK && (p_lit | p_mlen) == 0 && serial_rounds == 0 && bend - ip >= kSpecMin) {
+            // ================= table round: up to kSpan stream bytes of the block =================
+            const uintptr_t a_ip = reinterpret_cast<uintptr_t>(src) + ip;
+            const uintptr_t wbase = a_ip & ~(uintptr_t)15;
+            const uint32_t a0 = (uint32_t)(a_ip - wbase);         // window byte of stream position ip
+            const uint32_t bend_w = bend - ip + a0;                // window byte of the block end (may lie beyond the window)
+            const uint32_t nseg = min(32u, (min(bend_w, kSpan) + kSeg - 1) / kSeg);
+            __syncwarp();  // the previous round's list is read until its last execute step
             stage_window(ws, wbase, comp_hi, lane);
-            const uint32_t wofs = (uint32_t)(a0 - wbase) - ip;
             cp_async_wait_all();
             __syncwarp();
 
-            // ---- parse: lane k walks segment k
-            uint32_t pos = ip + lane * kSeg, cnt = 0;
-            uint32_t used = 0;  // pool slots handed out (uniform; may run past kPool, the excess is not stored)
-            const uint32_t lt = (1u << lane) - 1;
-            const uint32_t segend = min(pos + kSeg, spanend);
-            bool run = lane < nseg;  // chain alive (not stopped by something unusual)
-#if ZG_PREROLL > 0
-            // Run-up: lanes 1.. start up to ZG_PREROLL bytes before their segment and walk into it without recording,
-            // so that most chains are already on true boundaries when their segment begins and the chain before them
-            // joins within a hop or two (fewer join iterations, fewer speculative records in the pool).
-            {
-                const uint32_t seg0 = pos;
-                uint32_t pp = lane * kSeg > ZG_PREROLL ? seg0 - ZG_PREROLL : ip;
-#pragma unroll 1
-                for (uint32_t it = 0; it < ZG_PREROLL / 2; it++) {
-                    const bool act = run && lane != 0 && pp < seg0;
-                    if (!__any_sync(kFull, act)) break;
-                    if (act) {
-                        const Hop h = spec_hop(src, win, wofs, pp, bend);
-                        pp = h.ok ? h.nip : seg0;  // a dead run-up falls back to the segment's first byte
-                    }
-                }
-                if (lane != 0 && pp > seg0) pos = pp;
-            }
-#endif
-#pragma unroll 1
-            for (uint32_t it = 0; it < kCap; it++) {
-                const bool act = run && pos < segend;
-                if (!__any_sync(kFull, act)) break;
-                Hop h;
-                h.ok = false;
-                if (act) {
-                    h = spec_hop(src, win, wofs, pos, bend);
-                    if (!h.ok) run = false;
-                }
-                const uint32_t m = __ballot_sync(kFull, h.ok);
-                const uint32_t slot = used + __popc(m & lt);
-                used += __popc(m);
-                if (h.ok) {
-                    if (slot < kPool) {
-                        ws.pool[slot] = make_uint2((pos - ip) | (h.lit << 16), h.ml | (h.off << 16));
-                        ws.meta[slot] = (uint16_t)((lane << 8) | cnt);
-                        atomicOr(&ws.bmp[(pos - ip) >> 5], 1u << ((pos - ip) & 31));
-                        cnt++;
-                        pos = h.nip;
-                    } else
-                        run = false;  // pool exhausted: the chain stops here
-                }
-            }
+            // ---- tables: every lane its own segment (lanes past the block end have nothing to do)
+            const uint32_t seg0 = lane * kSeg, segend = seg0 + kSeg;
+            if (lane < nseg) build_tables(ws, seg0, bend_w);
             __syncwarp();
-            // ---- join: walk on into the following segments until a position their own chain visited
-            uint32_t nxt = 32, nj = 0;
-            bool seek = run && pos >= segend && pos < spanend;
-#pragma unroll 1
-            for (uint32_t e = 0; e <= kJoinHops; e++) {
-                if (!__any_sync(kFull, seek)) break;
-                Hop h;
-                h.ok = false;
-                if (seek) {
-                    const uint32_t b = pos - ip;
-                    if ((ws.bmp[b >> 5] >> (b & 31)) & 1u) {  // joined
-                        nxt = b / kSeg;
-                        seek = false;
-                    }
-                    else if (e == kJoinHops || used >= kPool) seek = false;  // the round ends at pos
-                    else {
-                        h = spec_hop(src, win, wofs, pos, bend);
-                        if (!h.ok) run = seek = false;
-                    }
-                }
-                const uint32_t m = __ballot_sync(kFull, h.ok);
-                const uint32_t slot = used + __popc(m & lt);
-                used += __popc(m);
-                if (h.ok) {
-                    if (slot < kPool) {
-                        ws.pool[slot] = make_uint2((pos - ip) | (h.lit << 16), h.ml | (h.off << 16));
-                        ws.meta[slot] = (uint16_t)((lane << 8) | cnt);
-                        cnt++;
-                        pos = h.nip;
-                        if (pos >= spanend) seek = false;
-                    } else
-                        seek = false;
-                }
-            }
-            if (nxt < 32) {
-                // the record joined is number (visited positions of its segment below the join) of its lane
-                const uint32_t lo = nxt * kSeg, hi = pos - ip;  // bits [lo, hi) of the map; hi - lo < kSeg
-#pragma unroll
-                for (uint32_t w = 0; w < 4; w++) {
-                    const uint32_t wi = (lo >> 5) + w, b0 = wi << 5;
-                    uint32_t bits = (wi < kSpanMax / 32 && b0 < hi) ? ws.bmp[wi] : 0u;
-                    if (b0 < lo) bits &= ~0u << (lo - b0);
-                    if (hi - b0 < 32u) bits &= (1u << (hi - b0)) - 1u;
-                    nj += __popc(bits);
-                }
-            }
-            // the next round takes fewer segments when this one ran out of record slots, more when it used few
-            if (used > kPool) seglim = seglim > 12 ? seglim - 8 : 4;
-            else if (used < kPool * 5 / 8 && seglim < 32) seglim += 4;
             ZG_T(t_parse);
-#ifdef ZG_LZ4_PROFILE
-            n_parsed += __reduce_add_sync(kFull, cnt);
-#endif
-            // ---- resolve: which lanes lie on the chain that starts at lane 0
-            uint32_t jump = nxt, reach = 1u << lane;
-#pragma unroll
-            for (int d = 0; d < 5; d++) {
-                const uint32_t jr = __shfl_sync(kFull, reach, jump & 31), jj = __shfl_sync(kFull, jump, jump & 31);
-                if (jump < 32) { reach |= jr; jump = jj; }
-            }
-            const uint32_t truemask = __shfl_sync(kFull, reach, 0);
-            const bool istrue = (truemask >> lane) & 1;
-            if (istrue && nxt < 32) ws.sj[nxt] = nj;
-            __syncwarp();
-            const uint32_t first = (istrue && lane != 0) ? ws.sj[lane] : 0u;
-            const uint32_t tc = istrue ? cnt - first : 0u;
-            const uint32_t incl = warp_incl_scan(tc, lane);
-            const uint32_t T = __shfl_sync(kFull, incl, 31);
-            ws.first[lane] = first;
-            ws.base[lane] = istrue ? (int32_t)(incl - tc) - (int32_t)first : kNotTrue;
-            __syncwarp();
-            const uint32_t nrec = min(used, kPool);
-#pragma unroll 1
-            for (uint32_t sl = lane; sl < nrec; sl += 32) {
-                const uint32_t mt = ws.meta[sl], k = mt >> 8, q = mt & 255u;
-                const int32_t b = ws.base[k];
-                if (b != kNotTrue && q >= ws.first[k]) ref[b + (int32_t)q] = (uint16_t)sl;
-            }
-            const uint32_t next_ip = __shfl_sync(kFull, pos, 31 - __clz(truemask));
-            __syncwarp();
-            const bool stopped = !__shfl_sync(kFull, run, 31 - __clz(truemask));  // the true chain met something unusual
-            ZG_T(t_res);
 
-            // ---- execute: kNP x 32 consecutive true sequences per step
+            // ---- compose: carry the true chain from segment to segment (uniform; one look-up per segment)
+            uint32_t e = a0, entry = kNone, stop_seg = 32;
+#pragma unroll 1
+            for (uint32_t k = 0; k < nseg; k++) {
+                const uint32_t kend = (k + 1) * kSeg;
+                if (e >= kend) continue;  // a long sequence jumped this segment
+                if (lane == k) entry = e;
+                const uint32_t x = ws.ex[e];
+                if (x == kStop) { stop_seg = k; break; }
+                e = kend + x;
+            }
+            __syncwarp();  // the exit table is dead from here: its space becomes the position slots
+
+            // ---- chain walk: each lane lists the true token positions of its segment, then all in stream order
+            uint32_t p = entry, cnt = 0;
+#pragma unroll 1
+            for (uint32_t it = 0; it < kSeg / 3 + 1; it++) {
+                const bool act = p < segend;  // entry == kNone: never
+                if (!__any_sync(kFull, act)) break;
+                if (act) {
+                    const uint32_t d = ws.nxt[p];
+                    if (d == 0) p |= 0x80000000u;  // stopped here (only the lane of stop_seg gets here)
+                    else { slots[lane * kSlots + cnt] = (uint16_t)p; cnt++; p += d; }
+                }
+            }
+            const uint32_t incl = warp_incl_scan(cnt, lane);
+            const uint32_t T = __shfl_sync(kFull, incl, 31);
+            const bool stopped = stop_seg < 32;
+            // where the stream goes on: in front of the sequence that stopped the chain, or where the chain left the span
+            const uint32_t next_w = stopped ? (__shfl_sync(kFull, p, stop_seg & 31) & 0x7fffffffu) : e;
+            __syncwarp();  // every lane is done reading the hop table: its space becomes the list
+            {
+                const uint32_t base = incl - cnt;
+                for (uint32_t j = 0; j < cnt; j++) list[base + j] = slots[lane * kSlots + j];
+            }
+            __syncwarp();
+            ZG_T(t_res);
+#ifdef ZG_LZ4_PROFILE
+            n_parsed += nseg * kSeg;
+#endif
+
+            // ---- execute: 32 consecutive true sequences per step
             const uint32_t ip0 = ip;
             uint32_t gop = op;
             bool bad = false;
 #pragma unroll 1
             for (uint32_t g0 = 0; g0 < T && !bad; g0 += 32 * kNP) {
-                uint32_t prel[kNP], lit[kNP], ml[kNP], off[kNP], dst[kNP], lit_src[kNP];
+                uint32_t prel[kNP], lit[kNP], ml[kNP], off[kNP], dst[kNP], lit_src[kNP], lit_w[kNP];
                 const uint32_t step0 = gop;
 #pragma unroll
                 for (int q = 0; q < kNP; q++) {
                     const uint32_t r = g0 + 32 * q + lane;
-                    prel[q] = lit[q] = ml[q] = off[q] = 0;
+                    prel[q] = lit[q] = ml[q] = off[q] = lit_src[q] = lit_w[q] = 0;
                     if (r < T) {
-                        const uint2 rec = ws.pool[ref[r]];
-                        prel[q] = rec.x & 0xffffu; lit[q] = rec.x >> 16; ml[q] = rec.y & 0xffffu; off[q] = rec.y >> 16;
+                        const uint32_t w = list[r];
+                        seq_at(win, w, lit[q], ml[q], off[q], lit_w[q]);
+                        prel[q] = w - a0;
+                        lit_src[q] = ip0 + lit_w[q] - a0;
                     }
                 }
 #pragma unroll
@@ -711,17 +607,21 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
                         if ((int)lane >= fa) lit[q] = ml[q] = 0;
                     }
                     gop += adv;
-                    // literals follow the token and the length-extension bytes (one per 255, plus the closing one)
-                    lit_src[q] = ip0 + prel[q] + 1 + (lit[q] >= 15u ? (lit[q] - 15u) / 255u + 1u : 0u);
                 }
-                exec_group<kNP>(src, lz, step0, lit_src, lit, ml, off, dst, lane);
+                exec_group<kNP, true>(src, win, lz, step0, lit_src, lit_w, lit, ml, off, dst, lane);
 #ifdef ZG_LZ4_PROFILE
                 for (int q = 0; q < kNP; q++) n_true += __popc(__ballot_sync(kFull, (lit[q] | ml[q]) != 0));
 #endif
             }
             op = gop;
-            if (!bad) ip = next_ip;
-            if (bad || T == 0 || stopped) force_serial = true;
+            if (!bad) ip = ip0 + next_w - a0;
+            // A round that stopped early (a sequence the table does not hold, the block's last sequence, an error) hands
+            // over to the serial walker; if that keeps happening the walker gets longer turns (long runs, long matches).
+            if (bad || stopped) {
+                serial_rounds = T >= 64 ? 1 : backoff;
+                backoff = T >= 64 ? 1 : min(backoff * 2, 16u);
+            } else
+                backoff = 1;
             ZG_T(t_exec);
 #ifdef ZG_LZ4_PROFILE
             n_spec++;
@@ -733,7 +633,7 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
         uint32_t cnt = 0;
         const uint32_t op_start = op;
         bool finished = false;  // chunk complete (ok or error) after this round's records
-        force_serial = false;
+        if (serial_rounds) serial_rounds--;
 #define ZG_EMIT(LSRC, LIT, ML, OFF)                                                                  \
     do {                                                                                             \
         if (lane == 0) {                                                                             \
@@ -889,7 +789,7 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
                 const uint32_t sc = warp_incl_scan(len, lane);
                 const uint32_t a_src[1] = {lit_src}, a_lit[1] = {lit}, a_off[1] = {off}, a_dst[1] = {op_start + sc - len};
                 uint32_t a_ml[1] = {ml};
-                exec_group<1>(src, lz, op_start, a_src, a_lit, a_ml, a_off, a_dst, lane);
+                exec_group<1, false>(src, win, lz, op_start, a_src, a_src, a_lit, a_ml, a_off, a_dst, lane);
                 __syncwarp();  // srec is rewritten next round
             }
         }
