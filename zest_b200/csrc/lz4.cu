@@ -62,7 +62,11 @@ constexpr uint32_t kMaxPiece = 65535;
 #ifndef ZG_NP
 #define ZG_NP 1
 #endif
+#ifndef ZG_TABLE_UNROLL
+#define ZG_TABLE_UNROLL 1
+#endif
 constexpr int kNP = ZG_NP;            // groups of 32 sequences per execute step
+constexpr int kTableUnroll = ZG_TABLE_UNROLL;  // words of a segment per trip of the table loop
 constexpr uint32_t kSerialCap = 16;   // sequences per round of the serial walker
 constexpr uint32_t kSeg = 68;          // stream bytes per lane and round: 17 words, so 32 lanes start in 32 banks
 constexpr uint32_t kSpan = 32 * kSeg;  // stream bytes parsed per round
@@ -180,8 +184,10 @@ __device__ __forceinline__ void warp_copy(uint8_t* dst, const uint8_t* src, uint
     const uint32_t* sw = reinterpret_cast<const uint32_t*>(sa & ~(uintptr_t)3);
     uint32_t* dw = reinterpret_cast<uint32_t*>(dst);
     if (sh == 0) {
+#pragma unroll 4
         for (uint32_t k = lane; k < nw; k += 32) dw[k] = SRC_IS_OUTPUT ? sw[k] : __ldg(sw + k);
     } else {
+#pragma unroll 4
         for (uint32_t k = lane; k < nw; k += 32) {
             uint32_t lo = SRC_IS_OUTPUT ? sw[k] : __ldg(sw + k);
             uint32_t hi = SRC_IS_OUTPUT ? sw[k + 1] : __ldg(sw + k + 1);
@@ -223,6 +229,7 @@ __device__ __forceinline__ void warp_regroup(uint8_t* out, const uint8_t* tmp, u
     const uint32_t p1 = q + (0 < r), p2 = p1 + q + (1 < r), p3 = p2 + q + (2 < r);
     const uint32_t q4 = q >> 2;  // groups of four quads = 16 output bytes
     const uint32_t oa = (uint32_t)(reinterpret_cast<uintptr_t>(out) & 15);
+#pragma unroll 4
     for (uint32_t g = lane; g < q4; g += 32) {
         const uint32_t j = 4 * g;
         const uint32_t a = ld4_unaligned(tmp + j), b = ld4_unaligned(tmp + p1 + j), c = ld4_unaligned(tmp + p2 + j),
@@ -291,7 +298,10 @@ __device__ __forceinline__ void build_tables(WarpShared& ws, uint32_t seg0, uint
     const uint32_t* const ww = reinterpret_cast<const uint32_t*>(ws.win) + seg0 / 4;
     const uint32_t segend = seg0 + kSeg;
     uint32_t hi = ww[kSeg / 4];
-#pragma unroll
+    // One word (four positions) per trip: unrolling all 17 would put ~3,000 instructions in the hot loop of 24 warps
+    // that are each somewhere else in the kernel, and the instruction cache does not hold that (measured: "no
+    // instruction" became the top stall reason).
+#pragma unroll kTableUnroll
     for (int i = kSeg / 4 - 1; i >= 0; i--) {
         const uint32_t cur = ww[i];
         uint32_t packed = 0;
