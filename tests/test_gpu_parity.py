@@ -574,3 +574,49 @@ def test_config2_full_size_roundtrip(ctx, oracle):
     bad = bytearray(blobs[3]); bad[len(bad) // 2] ^= 2; blobs[3] = bytes(bad)
     res2 = z.verify_xorbs(blobs, [x.expected for x in xs], ctx=ctx)
     assert [int(v == 1) for v in res2.verdict] == [int(i != 3) for i in range(len(xs))]
+
+
+def test_config3_bg4_at_scale(ctx, oracle):
+    """BASELINE.json configs[2] kind of input at a size that means something for scheme 2 (2 GiB of bf16, BG4-LZ4, 32
+    xorbs, ~33 k chunks; bench.py repeats this check on the full 16 GB): every verdict, every root and every chunk hash
+    against the oracle's, through the host-buffer call; one whole xorb reconstructed bit-exact; one damaged byte caught."""
+    from concurrent.futures import ThreadPoolExecutor
+    n_x, raw = 32, 64 << 20
+    with ThreadPoolExecutor(16) as ex:
+        built = list(ex.map(lambda i: oracle.synth_xorb("bf16", raw, 9000 + i, 2), range(n_x)))
+    blobs = [b[0] for b in built]
+    expected = np.frombuffer(b"".join(b[1] for b in built), np.uint8).reshape(-1, 32)
+    gold = np.concatenate([b[2] for b in built])
+    assert all(int(np.frombuffer(bl[:8], np.uint8)[4]) == 2 for bl in blobs)  # scheme byte of the first chunk header
+    res = z.verify_xorbs(blobs, expected, want_chunk_hashes=True, ctx=ctx)
+    assert res.ok and res.bytes_verified == n_x * raw
+    assert np.array_equal(res.roots, expected) and np.array_equal(res.chunk_hashes, gold)
+    k = 17
+    want = oracle.synth_bf16_fast(raw, 9000 + k)
+    got = z.XorbReader(blobs[k], ctx).extract_chunk_range(0, built[k][3].size)
+    assert got == want.tobytes()
+    bad = blobs[5].copy(); bad[bad.size // 3] ^= 0x10
+    res2 = z.verify_xorbs([bad], expected[5:6], ctx=ctx)
+    assert res2.verdict[0] != 1
+
+
+def test_config4_cdc_every_boundary_at_16GB(ctx, oracle):
+    """BASELINE.json configs[3]: Gearhash CDC of one 16 GB bf16 shard -- the size changes the kernel's segment geometry
+    (1,024 segments of 512 tiles instead of 512 x 64 at 1 GiB) -- with EVERY boundary compared with the oracle's serial
+    chunker (~10 s on the host), then every chunk hash on a 2 GB slice."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    if torch.cuda.mem_get_info(0)[0] < 40 << 30:
+        pytest.skip("needs 40 GB of free device memory")
+    n = 16_000_000_000
+    piece = 256 << 20
+    data = np.empty(n, np.uint8)
+    with ThreadPoolExecutor(16) as ex:
+        list(ex.map(lambda k: oracle.synth_bf16_fast(min(piece, n - k * piece), 333 + k, out=data[k * piece:k * piece + min(piece, n - k * piece)]),
+                    range((n + piece - 1) // piece)))
+    ends = z.cdc(data, ctx=ctx)
+    gold = oracle.cdc(data)
+    assert ends.size == gold.size and np.array_equal(ends, gold)
+    m = int(np.searchsorted(gold, 2_000_000_000))
+    off = np.concatenate([[0], gold[:m]]).astype(np.uint64)
+    assert np.array_equal(z.hash_chunks(data, off, ctx=ctx), oracle.hash_chunks(data, off, threads=16))

@@ -14,21 +14,28 @@ import sys
 # (region name, regex that matches the region's FIRST source line); order = order in lz4.cu
 MARKERS = [
     ("rd8/xxh/load_window", r"^__device__ __forceinline__ uint32_t rd8"),
-    ("load16", r"^template <bool READ_ONLY, int K>"),
+    ("load16 (global)", r"^template <bool READ_ONLY, int K>"),
+    ("load16_win (smem)", r"^template <int K>\s*$|^// The same from the staged stream window"),
     ("store16", r"^template <int I>"),
     ("warp_copy", r"^// Whole-warp copy of non-overlapping ranges"),
     ("warp_match", r"^// Whole-warp LZ4 match copy"),
     ("regroup", r"^// Four bytes at any alignment"),
     ("cp_async/stage", r"^__device__ __forceinline__ void cp_async16"),
+    ("tables (hop + exit)", r"^// Hop table \+ exit table"),
+    ("seq_at", r"^// The sequence at window byte w"),
     ("hop fast", r"^struct Hop"),
     ("hop general", r"^__device__ __noinline__ Hop spec_hop_general\(.*\{"),
     ("match_rounds", r"^// The matches of up to 32 sequences in stream order"),
     ("exec_group", r"^// One execute step"),
+    ("output ring", r"^// Output ring\."),
     ("scan", r"^__device__ __forceinline__ uint32_t warp_incl_scan"),
     ("kernel head+refill", r"^__global__ void __launch_bounds__\(32"),
-    ("spec: stage+run-up+parse loop", r"// =+ speculative round =+"),
+    ("round: stage", r"// =+ (speculative|table) round"),
+    ("spec: stage+run-up+parse loop", r"// ---- parse: lane k walks"),
     ("join", r"// ---- join:"),
     ("resolve", r"// ---- resolve:"),
+    ("compose", r"// ---- compose:"),
+    ("chain walk + list", r"// ---- chain walk:"),
     ("exec loop", r"// ---- execute:"),
     ("serial", r"// =+ serial round"),
     ("finish+regroup call", r"// ---- chunk finished this round"),
