@@ -168,6 +168,11 @@ typedef struct zg_chunk_desc { /* one per chunk; fill from zg_xorb_index (src_of
  * finish alone.  No counterpart in zest (scheduling detail of the GPU decoder). */
 ZG_API void zg_chunk_order(zg_chunk_desc* descs, size_t n);
 
+/* Chunk hashes on the device.  The scratch is sized from data_bytes and n, while the chunk lengths are read on the device:
+ * the chunks must not overlap and their lengths must add up to at most data_bytes (true for anything laid out by
+ * zg_xorb_index / zg_dev_cdc).  Lengths that add up to more are not allowed to write past the scratch: the kernels clamp
+ * to the capacity they were sized for and the chunks that did not fit come out as 32 zero bytes (which fails any
+ * verification) -- the same holds for zg_dev_hash_chunks_static and for the ulen fields given to zg_dev_verify_xorbs. */
 ZG_API size_t zg_dev_hash_scratch_bytes(uint64_t data_bytes, size_t n);
 ZG_API int zg_dev_hash_chunks(zg_ctx* ctx, const uint8_t* d_data, uint64_t data_bytes, const uint64_t* d_offsets,
                        const uint32_t* d_lens /* NULL: lens from offsets[i+1]-offsets[i] */, size_t n,
