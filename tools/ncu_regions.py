@@ -52,8 +52,21 @@ def main():
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "Line No")
     hdr = rows[hi]
     c_samp, c_inst = hdr.index("# Samples"), hdr.index("Instructions Executed")
-    lines = []  # (line no, source, samples, instructions)
-    for r in rows[hi + 1:]:
+    lines = []  # (line no, source, samples, instructions) of the FIRST file section (the kernel's own .cu file)
+    other = {}  # later sections: inlined code from CUDA headers (shuffles, votes, funnel shifts), totals per file
+    section = None
+    for r in rows:
+        if r and r[0] == "File Path":
+            section = r[1]
+            continue
+        if section is not None and section != rows[0][1]:
+            if r and r[0].strip().isdigit():
+                try:
+                    o = other.setdefault(section.split("/")[-1], [0.0, 0.0])
+                    o[0] += float(r[c_samp]); o[1] += float(r[c_inst])
+                except (ValueError, IndexError):
+                    pass
+            continue
         if r and r[0].strip().isdigit():
             def num(v):
                 try:
@@ -72,8 +85,8 @@ def main():
         if ln is not None:
             starts.append((ln, name))
     starts.sort()
-    tot_s = sum(x[2] for x in lines) or 1.0
-    tot_i = sum(x[3] for x in lines) or 1.0
+    tot_s = (sum(x[2] for x in lines) + sum(o[0] for o in other.values())) or 1.0
+    tot_i = (sum(x[3] for x in lines) + sum(o[1] for o in other.values())) or 1.0
     print(f"{rows[1][1][:120] if len(rows) > 1 and len(rows[1]) > 1 else ''}")
     print(f"total: {tot_s:.0f} stall samples, {tot_i:.4g} warp instructions")
     for k, (ln, name) in enumerate(starts):
@@ -81,6 +94,8 @@ def main():
         s = sum(x[2] for x in lines if ln <= x[0] < end)
         i = sum(x[3] for x in lines if ln <= x[0] < end)
         print(f"{name:32s} lines {ln}-{min(end, listing[-1][0] + 1) - 1}: stall samples {s / tot_s:.3f}  instructions {i / tot_i:.3f}")
+    for f, o in sorted(other.items(), key=lambda kv: -kv[1][1]):
+        print(f"{'(inlined from ' + f + ')':60s} stall samples {o[0] / tot_s:.3f}  instructions {o[1] / tot_i:.3f}")
     if top:
         print(f"\nhottest {top} source lines by instructions:")
         for l, s, sm, it in sorted(lines, key=lambda x: -x[3])[:top]:
