@@ -104,13 +104,15 @@ __device__ uint32_t xxh32_small(const uint8_t* p, uint32_t len) {
     return h;
 }
 
-// Eight stream bytes at any alignment as one u64 (three aligned word loads, issued together).  May touch the
-// aligned words just past p + 7; the compressed buffer is padded by 16 bytes for that.
-__device__ __forceinline__ uint64_t load_window(const uint8_t* p) {
+// Eight stream bytes at any alignment as one u64 (three aligned word loads, issued together).  Touches the aligned
+// words up to 11 bytes past p; `hi` is the end of what may be read (the compressed buffer rounded up to 16 bytes, which
+// the ABI asks callers to keep readable): words at or beyond it read as zero, so nothing past `hi` is ever touched.
+__device__ __forceinline__ uint64_t load_window(const uint8_t* p, const uint8_t* hi) {
     uintptr_t a = reinterpret_cast<uintptr_t>(p);
     const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+    const uint32_t* h = reinterpret_cast<const uint32_t*>(hi);
     uint32_t sh = (uint32_t)(a & 3) * 8;
-    uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    uint32_t w0 = w < h ? __ldg(w) : 0u, w1 = w + 1 < h ? __ldg(w + 1) : 0u, w2 = w + 2 < h ? __ldg(w + 2) : 0u;
     return (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
 }
 
@@ -131,6 +133,13 @@ __device__ __forceinline__ uint32_t ld_word_if(unsigned long long w, uint32_t sp
 }
 template <bool READ_ONLY>
 __device__ __forceinline__ void load16(const uint8_t* s, uint32_t n, uint32_t (&x)[4]) {
+#ifdef ZG_DIAG_FAST_LOADS  // timing experiment only (output is wrong): no global load, the address stands in for the data
+    if (!READ_ONLY) {
+        const uint32_t v = (uint32_t)reinterpret_cast<uintptr_t>(s) * 2654435761u + n;
+        x[0] = v; x[1] = v >> 3; x[2] = v >> 7; x[3] = v >> 11;
+        return;
+    }
+#endif
     const uintptr_t a = reinterpret_cast<uintptr_t>(s);
     const unsigned long long w = __cvta_generic_to_global(reinterpret_cast<const void*>(a & ~(uintptr_t)3));
     const uint32_t sh = (uint32_t)(a & 3) * 8, span = n ? (uint32_t)(a & 3) + n : 0;
@@ -163,6 +172,10 @@ __device__ __forceinline__ void st_byte_if(unsigned long long g, uint32_t n, uin
                  :: "r"(n), "n"(I), "l"(g), "r"(word >> (8 * (I & 3))) : "memory");
 }
 __device__ __forceinline__ void store16(uint8_t* d, uint32_t n, const uint32_t (&x)[4]) {
+#ifdef ZG_DIAG_FAST_STORES  // timing experiment only (output is wrong): one aligned word store instead of n byte stores
+    if (n) *reinterpret_cast<uint32_t*>(reinterpret_cast<uintptr_t>(d) & ~(uintptr_t)3) = x[0] ^ x[1] ^ x[2] ^ x[3];
+    return;
+#endif
     const unsigned long long g = __cvta_generic_to_global(d);
     st_byte_if<0>(g, n, x[0]); st_byte_if<1>(g, n, x[0]); st_byte_if<2>(g, n, x[0]); st_byte_if<3>(g, n, x[0]);
     st_byte_if<4>(g, n, x[1]); st_byte_if<5>(g, n, x[1]); st_byte_if<6>(g, n, x[1]); st_byte_if<7>(g, n, x[1]);
@@ -658,7 +671,7 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
                 // literal run and offset usually all sit inside it).
                 if (ip >= bend) { err = E_LZ4_BLOCK; finished = true; continue; }
                 const uint32_t ip0 = ip;
-                const uint64_t w8 = load_window(src + ip0);
+                const uint64_t w8 = load_window(src + ip0, comp_hi);
                 const uint32_t tok = (uint32_t)w8 & 0xffu;
                 ip++;
                 uint32_t lit = tok >> 4;
