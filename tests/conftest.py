@@ -120,6 +120,11 @@ def craft_lz4_block(rng, target_len: int, style: str):
         if style == "tiny":
             lit_n = int(rng.integers(0, 4))
             mlen = int(rng.integers(4, 9))
+        elif style == "edge":
+            # around what the decoder's hop table holds: a sequence of up to 255 stream bytes (token, one length byte
+            # each, literals, offset) -- literal runs of 225-260 bytes, match lengths of 255-300, and short ones between
+            lit_n = int(rng.choice([0, 3, 14, 15, 16, int(rng.integers(225, 261)), int(rng.integers(225, 261))]))
+            mlen = int(rng.choice([4, 18, 19, int(rng.integers(255, 301)), int(rng.integers(255, 301))]))
         elif style == "long":
             lit_n = int(rng.choice([0, 1, 15, 16, 17, 270, 271, 600, 70000]))
             mlen = int(rng.choice([4, 18, 19, 20, 21, 274, 275, 70000, 140000]))

@@ -198,7 +198,7 @@ def test_crafted_streams(ctx, oracle):
     rng = np.random.default_rng(78)
     records, wants = [], []
     for style, n in [("tiny", 5000), ("mixed", 60000), ("long", 900000), ("long", 300001), ("tiny", 9), ("mixed", 1),
-                     ("mixed", 131072), ("tiny", 70003), ("long", 2_000_000)]:
+                     ("mixed", 131072), ("tiny", 70003), ("long", 2_000_000), ("edge", 400_000), ("edge", 65_537)]:
         blk, want = craft_lz4_block(rng, n, style)
         frame = frame_single_block(blk, len(want))
         records.append(chunk_record(frame, 1, len(want))); wants.append(want)
