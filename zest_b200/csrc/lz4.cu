@@ -15,7 +15,7 @@
 //             for each of them, how long a sequence starting there would be (token, at most one length byte each,
 //             literals, offset) -- the HOP table, one byte per position, 0 where no such sequence fits -- and, walking
 //             its segment backwards, where the chain of hops from each position leaves the segment -- the EXIT table.
-//             The same ~40 instructions per position on every lane, whatever the data; nothing speculative, nothing
+//             The same ~30 instructions per position on every lane, whatever the data; nothing speculative, nothing
 //             thrown away, no dependent chain longer than two shared-memory reads.
 //   compose : the true chain enters segment 0 at the known position; one exit-table look-up per segment carries it
 //             across the round (32 dependent shared-memory reads, uniform across the warp), which gives every lane the
@@ -305,7 +305,7 @@ __device__ __forceinline__ void stage_window(WarpShared& ws, uintptr_t A, const 
 //            positional: the checks that need the output position are made at execute time.
 //   ex[w]  = where the chain of hops from w first leaves the segment, relative to the segment end (< kHopMax), or kStop
 //            if it runs into a 0 before that.  One look-up per segment then carries the true chain across the round.
-// Every position costs the same ~40 instructions on every lane, whatever the data: no speculation, nothing discarded.
+// Every position costs the same ~30 instructions on every lane, whatever the data: no speculation, nothing discarded.
 __device__ __forceinline__ void build_tables(WarpShared& ws, uint32_t seg0, uint32_t bend_w) {
     const uint8_t* const win = reinterpret_cast<const uint8_t*>(ws.win);
     const uint32_t* const ww = reinterpret_cast<const uint32_t*>(ws.win) + seg0 / 4;
