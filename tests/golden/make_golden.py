@@ -265,15 +265,33 @@ def term_kats():
     return out
 
 
+def bench_kats():
+    """The data kind of the bench workloads (oracle's table-driven bf16 generator, oz_synth_bf16_q16) at 256 MiB: xet-core's
+    file hash pins the oracle's CDC + chunk hashes + Merkle fold + file hash on exactly those bytes."""
+    sys.path.insert(0, os.path.join(HERE, "..", ".."))
+    from oracle.xet_oracle import synth_bf16_fast
+    out = []
+    for seed, n in ((7, 256 << 20), (1_000_003, 64 << 20)):
+        data = synth_bf16_fast(n, seed).tobytes()
+        fh = hash_file(data)
+        out.append({"name": f"bf16_q16_seed{seed}", "n_bytes": n, "seed": seed, "sha256": hashlib.sha256(data).hexdigest(), "file_hash": fh})
+        print(out[-1]["name"], fh)
+    return out
+
+
 def main():
     path = os.path.join(HERE, "vectors.json")
     if "--only-terms" in sys.argv:      # add the term vectors to an existing file without redoing the rest
         res = json.load(open(path))
         res["terms"] = term_kats()
+    elif "--only-bench" in sys.argv:    # the same for the bench-data vectors
+        res = json.load(open(path))
+        res["bench"] = bench_kats()
     else:
         res = {"generator": "tests/golden/make_golden.py", "hf_xet": "1.5.0", "blake3_pypi": "1.0.8",
                "gear_table_sha256": check_gear_table(),
-               "blake3": blake3_kats(), "xet": xet_kats(), "real_xorbs": real_xorbs(), "terms": term_kats()}
+               "blake3": blake3_kats(), "xet": xet_kats(), "real_xorbs": real_xorbs(), "terms": term_kats(),
+               "bench": bench_kats()}
     json.dump(res, open(path, "w"), indent=0)
     print("wrote", path)
 

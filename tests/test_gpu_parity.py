@@ -576,6 +576,16 @@ def test_config2_full_size_roundtrip(ctx, oracle):
     assert [int(v == 1) for v in res2.verdict] == [int(i != 3) for i in range(len(xs))]
 
 
+def test_bench_data_file_hash_on_gpu(ctx, oracle, vectors):
+    """The bytes of the bench workloads through the GPU seed path (CDC + chunk hashes + file hash in one call) against
+    hf_xet's file hash of the same bytes (tests/golden/vectors.json "bench"; the 64 MiB record is xorb 0 of the default set)."""
+    for rec in vectors["bench"]:
+        data = oracle.synth_bf16_fast(rec["n_bytes"], rec["seed"])
+        ends, hashes, fh = z.cdc_hash(data, ctx=ctx)
+        assert z.hash_to_hex(fh) == rec["file_hash"]
+        assert np.array_equal(ends, oracle.cdc(data))
+
+
 def test_config3_bg4_at_scale(ctx, oracle):
     """BASELINE.json configs[2] kind of input at a size that means something for scheme 2 (2 GiB of bf16, BG4-LZ4, 32
     xorbs, ~33 k chunks; bench.py repeats this check on the full 16 GB): every verdict, every root and every chunk hash

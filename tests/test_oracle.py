@@ -176,3 +176,17 @@ def test_range_hashes_against_hf_xet_shards(oracle, vectors):
         assert base == ends.size
         got = oracle.range_hashes(hashes, bounds)
         assert [g.tobytes().hex() for g in got] == [t["range_hash"] for t in rec["terms"]]
+
+
+def test_bench_data_file_hash(oracle, vectors):
+    """The bytes the bench workloads are made of (the oracle's fast bf16 generator; the 64 MiB record is xorb 0 of the
+    default 16 GB set): the generator reproduces them bit for bit, and the oracle's CDC + chunk hashes + Merkle fold +
+    file hash over them equal what hf_xet.hash_files reported when tests/golden/make_golden.py --only-bench ran."""
+    import hashlib
+    for rec in vectors["bench"]:
+        data = oracle.synth_bf16_fast(rec["n_bytes"], rec["seed"])
+        assert hashlib.sha256(data.tobytes()).hexdigest() == rec["sha256"]
+        ends = oracle.cdc(data)
+        off = np.concatenate([np.zeros(1, np.uint64), ends])
+        hashes = oracle.hash_chunks(data, off, threads=8)
+        assert oracle.hash_to_hex(oracle.file_hash(hashes, np.diff(off))) == rec["file_hash"]
