@@ -1,6 +1,7 @@
 """Parity of the CUDA path against the oracle and the golden vectors, through the C ABI (zest_b200 -> ctypes ->
 libzest_gpu.so).  Integer / byte work: every comparison is bit-exact.  Run on the B200 box: pytest -m gpu."""
 import hashlib
+import os
 
 import numpy as np
 import pytest
@@ -630,3 +631,37 @@ def test_config4_cdc_every_boundary_at_16GB(ctx, oracle):
     m = int(np.searchsorted(gold, 2_000_000_000))
     off = np.concatenate([[0], gold[:m]]).astype(np.uint64)
     assert np.array_equal(z.hash_chunks(data, off, ctx=ctx), oracle.hash_chunks(data, off, threads=16))
+
+
+def test_real_xet_core_xorbs_made_on_this_box(ctx, oracle):
+    """hf_xet (xet-core, the production implementation of the protocol) is in this image: let it chunk, compress
+    (lz4_flex, byte-grouped) and store 160 MiB of bf16 on the spot, then read the stored xorb files back as they lie on
+    disk (chunk stream + XETBLOB footer): content address = file name, chunk hashes = the footer's, reconstructed
+    bytes = the file.  tools/real_xorb_replay.py does the same at 2 GB with timing."""
+    hf_xet = pytest.importorskip("hf_xet")
+    import shutil
+    import tempfile
+    n = 160 << 20
+    data = oracle.synth_bf16_fast(n, 77077)
+    d = tempfile.mkdtemp(prefix="xetreplay")
+    os.environ["HF_XET_XORB_COMPRESSION_POLICY"] = "bg4-lz4"
+    try:
+        s = hf_xet.XetSession()
+        with s.new_upload_commit(endpoint="local://" + d) as c:
+            h = c.start_upload_bytes(data.tobytes())
+        file_hash = h.result().xet_info.hash
+        xdir = os.path.join(d, "xet", "xorbs", "xorbs")
+        files = sorted(os.listdir(xdir), key=lambda f: os.path.getmtime(os.path.join(xdir, f)))
+        raws = [(f.split(".", 1)[1], np.fromfile(os.path.join(xdir, f), np.uint8)) for f in files]
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+    assert len(raws) >= 2
+    expected = [z.hex_to_hash(name) for name, _ in raws]
+    res = z.verify_xorbs([r for _, r in raws], expected, want_chunk_hashes=True, ctx=ctx)
+    assert res.ok and res.bytes_verified == n
+    gold = np.concatenate([footer_chunk_hashes(r.tobytes())[0] for _, r in raws])
+    assert np.array_equal(res.chunk_hashes, gold)
+    out = b"".join(z.XorbReader(r, ctx).extract_chunk_range(0, z.xorb_index(r).n_chunks) for _, r in raws)
+    assert out == data.tobytes()
+    # and the whole file's Xet hash through the GPU seed path equals what xet-core reported for the upload
+    assert z.hash_to_hex(z.cdc_hash(data, ctx=ctx)[2]) == file_hash
