@@ -41,6 +41,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--bytes", type=int, default=2_000_000_000)
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--kind", default="bf16", choices=["bf16", "text"], help="bf16 -> policy bg4-lz4, text -> policy lz4")
     args = ap.parse_args()
     import hf_xet
     import torch
@@ -53,9 +54,12 @@ def main():
     data = np.empty(n, np.uint8)
     for k in range((n + piece - 1) // piece):
         m = min(piece, n - k * piece)
-        oz.synth_bf16_fast(m, 424242 + k, out=data[k * piece:k * piece + m])
+        if args.kind == "bf16":
+            oz.synth_bf16_fast(m, 424242 + k, out=data[k * piece:k * piece + m])
+        else:
+            data[k * piece:k * piece + m] = oz.synth_zipf_text(m, 424242 + k)
     d = tempfile.mkdtemp(prefix="xetreplay", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
-    os.environ["HF_XET_XORB_COMPRESSION_POLICY"] = "bg4-lz4"
+    os.environ["HF_XET_XORB_COMPRESSION_POLICY"] = "bg4-lz4" if args.kind == "bf16" else "lz4"
     try:
         t0 = time.time()
         s = hf_xet.XetSession()
@@ -158,7 +162,7 @@ def main():
     assert bool((d_verdict == 1).all()) and np.array_equal(d_hashes.cpu().numpy().reshape(-1, 32), gold)
     t_dec = timed(dec)
     print(json.dumps({
-        "what": "real xet-core xorbs (hf_xet local store, lz4_flex, policy bg4-lz4) replayed through libzest_gpu",
+        "what": f"real xet-core xorbs (hf_xet local store, lz4_flex, {args.kind} data, policy {os.environ['HF_XET_XORB_COMPRESSION_POLICY']}) replayed through libzest_gpu",
         "hf_xet_upload_seconds": round(t_up, 1), "file_hash": file_hash, "bytes": n, "xorbs": nx, "chunks": int(nchunks),
         "stored_bytes": int(stored), "ratio": round(sum(slen) / n, 4),
         "scheme_histogram": {str(k): int((schemes == k).sum()) for k in (0, 1, 2)},
