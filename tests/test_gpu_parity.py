@@ -665,3 +665,43 @@ def test_real_xet_core_xorbs_made_on_this_box(ctx, oracle):
     assert out == data.tobytes()
     # and the whole file's Xet hash through the GPU seed path equals what xet-core reported for the upload
     assert z.hash_to_hex(z.cdc_hash(data, ctx=ctx)[2]) == file_hash
+
+
+def test_device_hash_never_writes_past_its_scratch(ctx, oracle):
+    """zg_dev_hash_chunks sizes its scratch from the data_bytes the caller states, while the chunk lengths are read on the
+    device.  Lengths that add up to four times the stated bytes must not push the kernels past the scratch: the chunks
+    that fit hash correctly, the others come out as 32 zero bytes, and a guard region behind the scratch stays intact."""
+    import ctypes as C
+    import torch
+    from zest_b200 import _native
+    from zest_b200._native import check
+    L = _native.lib()
+    dev = torch.device("cuda", 0)
+    n, each = 100, 80_000
+    data = oracle.synth_random(n * each, 31)
+    off = (np.arange(n + 1, dtype=np.uint64) * np.uint64(each))
+    d_data = torch.from_numpy(np.concatenate([data, np.zeros(16, np.uint8)])).to(dev)
+    d_off = torch.from_numpy(off.view(np.int64)).to(dev)
+    stated = n * each // 4                                   # the caller understates the data size
+    need = L.zg_dev_hash_scratch_bytes(stated, n)
+    guard = 1 << 20
+    scratch = torch.full((need + guard,), 0xAB, dtype=torch.uint8, device=dev)
+    out = torch.full((32 * n,), 0xCD, dtype=torch.uint8, device=dev)
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    check(L.zg_dev_hash_chunks(ctx.handle, d_data.data_ptr(), stated, d_off.data_ptr(), None, n, None, out.data_ptr(),
+                               scratch.data_ptr(), need, stream))
+    torch.cuda.synchronize()
+    assert bool((scratch[need:] == 0xAB).all()), "the kernels wrote behind the scratch"
+    got = out.cpu().numpy().reshape(n, 32)
+    want = oracle.hash_chunks(data, off, threads=4)
+    good = [i for i in range(n) if np.array_equal(got[i], want[i])]
+    zero = [i for i in range(n) if not got[i].any()]
+    assert len(good) + len(zero) == n and good and zero
+    assert good == list(range(len(good)))                    # the chunks that fit are the leading ones
+    # with the true size stated, every chunk hashes
+    need2 = L.zg_dev_hash_scratch_bytes(n * each, n)
+    scratch2 = torch.empty(need2, dtype=torch.uint8, device=dev)
+    check(L.zg_dev_hash_chunks(ctx.handle, d_data.data_ptr(), n * each, d_off.data_ptr(), None, n, None, out.data_ptr(),
+                               scratch2.data_ptr(), need2, stream))
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().reshape(n, 32), want)
