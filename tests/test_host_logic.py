@@ -132,3 +132,37 @@ def test_native_partition_matches_the_python_mirror():
             assert sorted(i for p in got for i in p) == list(range(n))
             if n >= parts and len(set(s)) == 1:
                 assert max(map(len, got)) - min(map(len, got)) <= 1
+
+
+def test_bench_descriptors_follow_the_chunk_streams():
+    """bench.build_descs (the device-resident leg's chunk descriptors, built from zg_xorb_index on the host): payload
+    offsets, lengths and schemes equal the oracle's walk of the same blobs; decoded chunks are laid out back to back on
+    16-byte boundaries; `order` is a permutation that puts the longest chunks first (zg_chunk_order)."""
+    import numpy as np
+    import bench
+    from oracle import xet_oracle as oz
+    from zest_b200 import _native
+    old = bench.XORB_RAW
+    bench.XORB_RAW = 1 << 20
+    try:
+        xs, n_all, comp_all, _ = bench.build_xorb_set("llama8b-bg4", 3 * (1 << 20) + 777, 5, 0, 1, 2, lambda b: np.zeros(b, np.uint8),
+                                                      lambda a: a, lambda m: None)
+    finally:
+        bench.XORB_RAW = old
+    d, out_bytes = bench.build_descs(xs, _native.lib())
+    k = 0
+    for o, v in zip(xs.offsets, xs.views):
+        ix = oz.xorb_index(v)
+        m = ix.n
+        assert np.array_equal(d["src_off"][k:k + m], o + ix.hdr_off + 8)
+        assert np.array_equal(d["clen"][k:k + m], ix.clen) and np.array_equal(d["ulen"][k:k + m], ix.ulen)
+        assert np.array_equal(d["scheme"][k:k + m], ix.scheme)
+        k += m
+    assert k == d.size == int(xs.first[-1])
+    al = (d["ulen"].astype(np.int64) + 15) // 16 * 16
+    assert np.array_equal(d["dst_off"], np.concatenate([[0], np.cumsum(al)[:-1]])) and out_bytes == int(al.sum())
+    order = d["order"].astype(np.int64)
+    assert sorted(order.tolist()) == list(range(d.size))
+    size = d["clen"].astype(np.int64) + d["ulen"].astype(np.int64)
+    assert (np.diff(size[order]) <= 0).all()
+    assert bench.plan_xorbs(3 * (64 << 20) + 5) == [64 << 20] * 3 + [5] and bench.plan_xorbs(10) == [10]
