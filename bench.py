@@ -162,6 +162,13 @@ def build_xorb_set(name: str, nbytes: int, seed: int, rank: int, world: int, thr
     return s, n, int(sizes.sum()), [int(sum(sizes[i] for i in p)) for p in parts]
 
 
+def make_workload(name: str, nbytes: int, seed: int, threads: int):
+    """The whole set on one rank as plain arrays -> (blobs, expected (n,32) u8, chunk hashes, uncompressed bytes, chunks):
+    what the developer tools under tools/ take."""
+    xs, _, _, _ = build_xorb_set(name, nbytes, seed, 0, 1, threads, lambda b: np.zeros(b, np.uint8), lambda a: a, lambda m: None)
+    return xs.views, xs.expected, xs.hashes, xs.total, int(xs.first[-1])
+
+
 def build_descs(xs: XorbSet, L):
     """Chunk descriptors of the rank's set from the host walk (zg_xorb_index), vectorised; decoded chunks 16-byte aligned."""
     import zest_b200 as z

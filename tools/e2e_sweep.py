@@ -9,7 +9,7 @@ sys.path.insert(0, %r)
 import bench, zest_b200 as z
 blobs, expected, gold, total, nchunks = bench.make_workload(sys.argv[1], int(sys.argv[2]), 1, os.cpu_count())
 ctx = z.Context(0)
-host = ctx.pinned_empty(sum(len(b) for b in blobs) + 64)
+host = ctx.pinned_empty(int(sum(len(b) for b in blobs)) + 64)
 views, p = [], 0
 for b in blobs:
     host[p:p+len(b)] = np.frombuffer(b, np.uint8); views.append(host[p:p+len(b)]); p += len(b)
