@@ -328,6 +328,36 @@ def test_decode_fuzz_payload(ctx, oracle):
     assert (got.roots[ok] == want_roots[ok]).all()
 
 
+def test_decode_garbage_blocks(ctx, oracle):
+    """LZ4 blocks made of noise behind a valid frame header: thousands of byte strings that mean nothing go through the
+    hop tables, the chain walk and the execute step until some check stops them.  Nothing may hang or fault, and every
+    verdict -- which error, or that the noise happened to decode -- must be the oracle's.  Three kinds of noise: uniform
+    bytes, bytes biased to small values (short literal runs, long chains of sequences), and a valid stream's prefix with
+    noise after it."""
+    from conftest import chunk_record, craft_lz4_block, frame_single_block
+    rng = np.random.default_rng(9001)
+    good_blk, good_out = craft_lz4_block(rng, 60000, "mixed")
+    blobs = []
+    for i in range(4000):
+        kind = i % 3
+        n = int(rng.integers(32, 5000))
+        if kind == 0:
+            blk = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        elif kind == 1:
+            blk = (rng.integers(0, 256, n, dtype=np.uint8) & rng.choice([0x0f, 0x1f, 0x33, 0x77], n).astype(np.uint8)).tobytes()
+        else:
+            cut = int(rng.integers(16, len(good_blk) - 1))
+            blk = good_blk[:cut] + rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        ulen = int(rng.choice([1, 100, 8192, 65536, 131072, int(rng.integers(1, 200000))]))
+        blobs.append(chunk_record(frame_single_block(blk, ulen), 1 + (i // 3) % 2, ulen))
+    got = z.verify_xorbs(blobs, ctx=ctx)
+    want_v, want_roots, _ = oracle.verify_xorbs(blobs, threads=8)
+    assert list(got.verdict) == list(want_v)
+    ok = want_v >= 0
+    assert (got.roots[ok] == want_roots[ok]).all()
+    assert len(set(int(v) for v in want_v)) >= 2          # more than one kind of outcome
+
+
 def test_many_xorbs_batch(ctx, oracle):
     """A batch that spans several sub-batches and both pipeline lanes, mixed schemes, one corrupt in the middle."""
     blobs, expected = [], []
