@@ -356,6 +356,7 @@ def reference_arm(args, wl, out_stream):
             assert (v == 1).all() and nb == tot
         sample = f"{m} of {n_all} xorbs ({tot/1e6:.0f} MB uncompressed) per step, {'liblz4 block decoder' if lz else 'plain decoder'}"
         work = tot
+        config = dict(config, n_xorbs=n_all, compressed_bytes_total=comp_all, compression_ratio=round(comp_all / nbytes, 4))
     elif wl["mode"] == "hash":
         data = oz.synth_random(nbytes, 0)
         off = np.concatenate([np.zeros(1, np.uint64), oz.cdc(data)])
@@ -654,9 +655,9 @@ def verify_bench(args, wl, out_stream):
         "metric": METRIC, "value": round(value, 3), "unit": "GB/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": round(t_dev / K * 1e3, 4), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": dict(config, n_xorbs=n_all, compressed_bytes_total=comp_all, compression_ratio=round(comp_all / nbytes, 4),
-                       rank0={"xorbs": nx, "chunks": int(nchunks), "uncompressed_bytes": total, "compressed_bytes": comp_bytes},
-                       partition_compressed_bytes=part_bytes, generate_seconds=round(xs.gen_seconds, 1)),
+        "config": dict(config, n_xorbs=n_all, compressed_bytes_total=comp_all, compression_ratio=round(comp_all / nbytes, 4)),
+        "run": {"rank0": {"xorbs": nx, "chunks": int(nchunks), "uncompressed_bytes": total, "compressed_bytes": comp_bytes},
+                "partition_compressed_bytes": part_bytes, "generate_seconds": round(xs.gen_seconds, 1)},
         "e2e": dict({"value": round(e2e_val, 3), "unit": "GB/s", "ms_per_step": round(t_e2e / K * 1e3, 3),
                      "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) // K),
                      "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) // K),
