@@ -864,6 +864,26 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
         if (finished) {
             __syncwarp();
             if (err == 0 && scheme == 2) warp_regroup(fin_out, lz, ulen, lane);
+#ifdef ZG_DIAG_HASH_LOAD  // timing experiment only: integer work of the size and shape a BLAKE3 of the chunk would be
+            {             // (784 thread-instructions per 64 bytes per lane, four independent columns, add / xor / rotate), no loads
+                uint32_t va[4], vb[4], vc[4], vd[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) { va[k] = lane + ulen + k; vb[k] = va[k] * 3u; vc[k] = vb[k] ^ 0x9e3779b9u; vd[k] = vc[k] + 7u; }
+                const uint32_t iters = (uint32_t)(((uint64_t)(ulen / 32u) * 784u) / (64u * 48u));
+#pragma unroll 1
+                for (uint32_t it = 0; it < iters; it++) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        va[k] += vb[k]; vd[k] = __funnelshift_l(vd[k] ^ va[k], vd[k] ^ va[k], 16); vc[k] += vd[k]; vb[k] = __funnelshift_l(vb[k] ^ vc[k], vb[k] ^ vc[k], 12);
+                        va[k] += vb[k]; vd[k] = __funnelshift_l(vd[k] ^ va[k], vd[k] ^ va[k], 8);  vc[k] += vd[k]; vb[k] = __funnelshift_l(vb[k] ^ vc[k], vb[k] ^ vc[k], 7);
+                    }
+                }
+                uint32_t x = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++) x ^= va[k] ^ vb[k] ^ vc[k] ^ vd[k];
+                if (x == 0x12345678u) status[ci] = err;  // keeps the work alive (the value is the one lane 0 writes anyway)
+            }
+#endif
             if (lane == 0) status[ci] = err;
             state = ST_IDLE;
         }
