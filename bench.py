@@ -500,16 +500,17 @@ def verify_bench(args, wl, out_stream):
     d_out = torch.empty(out_bytes + 16, dtype=torch.uint8, device=dev)
     d_status = torch.zeros(max(nchunks, 1), dtype=torch.int32, device=dev)
     s_dec = torch.empty(L.zg_dev_decode_scratch_bytes(nchunks, out_bytes), dtype=torch.uint8, device=dev)
-    s_hash = torch.empty(L.zg_dev_hash_scratch_bytes(out_bytes, nchunks), dtype=torch.uint8, device=dev)
+    s_hash = torch.empty(L.zg_dev_hash_decoded_scratch_bytes(out_bytes, nchunks), dtype=torch.uint8, device=dev)
     s_mer = torch.empty(L.zg_dev_merkle_scratch_bytes(nchunks, nx), dtype=torch.uint8, device=dev)
 
+    # the stages as zg_dev_verify_xorbs runs them: byte-grouped chunks stay as planes, the hash regroups them as it reads
     def k_decode():
-        check(L.zg_dev_decode_chunks(ctx.handle, d_comp.data_ptr(), cpos, d_desc.data_ptr(), nchunks, d_out.data_ptr(), out_bytes,
-                                     d_status.data_ptr(), s_dec.data_ptr(), s_dec.numel(), sp))
+        check(L.zg_dev_decode_for_hash(ctx.handle, d_comp.data_ptr(), cpos, d_desc.data_ptr(), nchunks, d_out.data_ptr(), out_bytes,
+                                       d_status.data_ptr(), s_dec.data_ptr(), s_dec.numel(), sp))
 
     def k_hash():
-        check(L.zg_dev_hash_chunks(ctx.handle, d_out.data_ptr(), out_bytes, d_off.data_ptr(), d_len.data_ptr(), nchunks, None,
-                                   d_hashes.data_ptr(), s_hash.data_ptr(), s_hash.numel(), sp))
+        check(L.zg_dev_hash_decoded(ctx.handle, d_out.data_ptr(), out_bytes, d_desc.data_ptr(), nchunks, s_dec.data_ptr(),
+                                    d_hashes.data_ptr(), s_hash.data_ptr(), s_hash.numel(), sp))
 
     def k_merkle():
         check(L.zg_dev_merkle(ctx.handle, d_hashes.data_ptr(), d_len.data_ptr(), d_first.data_ptr(), nx, nchunks, d_status.data_ptr(),
@@ -517,11 +518,13 @@ def verify_bench(args, wl, out_stream):
 
     stages = {}
     ks = max(3, min(K, 5))
+    d_hashes.zero_()
     for name, fn in (("lz4_decode", k_decode), ("blake3_hash", k_hash), ("merkle_fold", k_merkle)):
         for _ in range(2):
             fn()
         stages[name] = timed(fn, ks) / ks
     assert int(d_status.abs().sum()) == 0 and bool((d_verdict[:nx] == 1).all())
+    assert np.array_equal(d_hashes.cpu().numpy().reshape(-1, 32)[:nchunks], xs.hashes), "stage-wise verify: chunk hashes"
     # what the link alone does: the same compressed bytes, pinned host -> device, nothing else (bounds e2e from above)
     for _ in range(2):
         d_comp[:cpos].copy_(pin_t, non_blocking=True)

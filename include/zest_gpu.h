@@ -197,13 +197,29 @@ ZG_API int zg_dev_decode_chunks(zg_ctx* ctx, const uint8_t* d_comp, uint64_t com
                          size_t n_chunks, uint8_t* d_out, uint64_t out_bytes, int32_t* d_status, void* d_scratch,
                          size_t scratch_bytes, void* stream);
 
+/* The two halves of zg_dev_verify_xorbs for a caller that only wants hashes, not bytes (and for measuring them apart).
+ * zg_dev_decode_for_hash is zg_dev_decode_chunks except that byte-grouped chunks (scheme 2 -- what safetensors xorbs use,
+ * CLAUDE.md:22) are NOT regrouped into d_out: their four byte planes stay in the decode scratch, and
+ * zg_dev_hash_decoded hashes them from there, interleaving the planes as it reads (the chunk hash is over the regrouped
+ * bytes either way).  That saves a read and a write of every decoded byte: 17 % of the decode time on bf16.  d_out holds
+ * the bytes of scheme-0/1 chunks only; dst_off must be a multiple of 16 (zg_xorb_index-style layouts are).  Pass the
+ * same d_chunks, out_bytes and decode scratch to both.  No counterpart in zest: XorbReader.extractChunkRange always
+ * materialises the bytes (src/xet_bridge.zig:256-257); verification has no use for them. */
+ZG_API int zg_dev_decode_for_hash(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes, const zg_chunk_desc* d_chunks,
+                           size_t n_chunks, uint8_t* d_out, uint64_t out_bytes, int32_t* d_status, void* d_scratch,
+                           size_t scratch_bytes, void* stream);
+ZG_API size_t zg_dev_hash_decoded_scratch_bytes(uint64_t out_bytes, size_t n);
+ZG_API int zg_dev_hash_decoded(zg_ctx* ctx, const uint8_t* d_out, uint64_t out_bytes, const zg_chunk_desc* d_chunks, size_t n_chunks,
+                        const void* d_decode_scratch, uint8_t* d_hashes, void* d_scratch, size_t scratch_bytes, void* stream);
+
 ZG_API size_t zg_dev_merkle_scratch_bytes(size_t n_chunks, size_t n_xorbs);
 /* d_first: n_xorbs + 1 chunk indices delimiting each xorb's chunks in d_hashes / d_lens. */
 ZG_API int zg_dev_merkle(zg_ctx* ctx, const uint8_t* d_hashes, const uint32_t* d_lens, const uint32_t* d_first,
                   size_t n_xorbs, size_t n_chunks, const int32_t* d_status, const uint8_t* d_expected,
                   uint8_t* d_roots, int8_t* d_verdict, void* d_scratch, size_t scratch_bytes, void* stream);
 
-/* decode -> hash -> fold -> compare in one call (the three calls above on one stream, sharing scratch). */
+/* decode -> hash -> fold -> compare in one call (zg_dev_decode_for_hash, zg_dev_hash_decoded and zg_dev_merkle on one
+ * stream, sharing scratch; the decoded bytes are not an output of this call). */
 ZG_API size_t zg_dev_verify_scratch_bytes(size_t n_chunks, size_t n_xorbs, uint64_t out_bytes);
 ZG_API int zg_dev_verify_xorbs(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes, const zg_chunk_desc* d_chunks,
                         size_t n_chunks, const uint32_t* d_first, size_t n_xorbs, const uint8_t* d_expected,

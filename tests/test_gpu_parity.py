@@ -291,6 +291,16 @@ def test_decode_chunk_size_sweep(ctx, oracle):
         off = np.concatenate([np.zeros(1, np.uint64), ends])
         root = oracle.merkle_root(oracle.hash_chunks(d, off), np.diff(off))
         assert z.verify_xorbs([blob], [root], ctx=ctx).ok
+    # every size as a byte-grouped chunk (a frame flag forces the framed form even where it is not smaller): verify
+    # hashes such chunks from their four planes without regrouping them first -- plane lengths n/4 + (k < n%4), planes
+    # starting at any alignment, blocks and leaves that end inside a plane
+    d = bf[:total]
+    blob = oracle.build_xorb(d, ends, 2, fflags=1)
+    assert set(oracle.xorb_index(blob).scheme.tolist()) == {2}
+    gold = oracle.hash_chunks(d, off)
+    res = z.verify_xorbs([blob], [oracle.merkle_root(gold, np.diff(off))], want_chunk_hashes=True, ctx=ctx)
+    assert res.ok and np.array_equal(res.chunk_hashes, gold)
+    assert z.XorbReader(blob, ctx).extract_chunk_range(0, len(sizes)) == d.tobytes()
 
 
 def test_decode_fuzz_payload(ctx, oracle):

@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warps", default="")
     ap.add_argument("--cdc", action="store_true")
+    ap.add_argument("--regroup", action="store_true", help="time the decode of the reconstruct path (byte-grouped chunks regrouped "
+                    "into the output) and the hash over plain bytes, instead of the verify path's halves")
     args = ap.parse_args()
     nbytes = args.bytes or bench.WORKLOADS[args.workload]["nbytes"]
     dev = torch.device("cuda", 0)
@@ -56,17 +58,23 @@ def main():
     d_roots = torch.zeros(32 * nx, dtype=torch.uint8, device=dev)
     d_verdict = torch.zeros(nx, dtype=torch.int8, device=dev)
     s_dec = torch.empty(L.zg_dev_decode_scratch_bytes(nchunks, out_bytes), dtype=torch.uint8, device=dev)
-    s_hash = torch.empty(L.zg_dev_hash_scratch_bytes(out_bytes, nchunks), dtype=torch.uint8, device=dev)
+    s_hash = torch.empty(max(L.zg_dev_hash_scratch_bytes(out_bytes, nchunks), L.zg_dev_hash_decoded_scratch_bytes(out_bytes, nchunks)),
+                         dtype=torch.uint8, device=dev)
     s_mer = torch.empty(L.zg_dev_merkle_scratch_bytes(nchunks, nx), dtype=torch.uint8, device=dev)
     sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     def k_decode():
-        check(L.zg_dev_decode_chunks(ctx.handle, d_comp.data_ptr(), cpos, d_desc.data_ptr(), nchunks, d_out.data_ptr(), out_bytes,
-                                     d_status.data_ptr(), s_dec.data_ptr(), s_dec.numel(), sp))
+        f = L.zg_dev_decode_chunks if args.regroup else L.zg_dev_decode_for_hash
+        check(f(ctx.handle, d_comp.data_ptr(), cpos, d_desc.data_ptr(), nchunks, d_out.data_ptr(), out_bytes,
+                d_status.data_ptr(), s_dec.data_ptr(), s_dec.numel(), sp))
 
     def k_hash():
-        check(L.zg_dev_hash_chunks(ctx.handle, d_out.data_ptr(), out_bytes, d_off.data_ptr(), d_len.data_ptr(), nchunks, None,
-                                   d_hashes.data_ptr(), s_hash.data_ptr(), s_hash.numel(), sp))
+        if args.regroup:
+            check(L.zg_dev_hash_chunks(ctx.handle, d_out.data_ptr(), out_bytes, d_off.data_ptr(), d_len.data_ptr(), nchunks, None,
+                                       d_hashes.data_ptr(), s_hash.data_ptr(), s_hash.numel(), sp))
+        else:
+            check(L.zg_dev_hash_decoded(ctx.handle, d_out.data_ptr(), out_bytes, d_desc.data_ptr(), nchunks, s_dec.data_ptr(),
+                                        d_hashes.data_ptr(), s_hash.data_ptr(), s_hash.numel(), sp))
 
     def k_merkle():
         check(L.zg_dev_merkle(ctx.handle, d_hashes.data_ptr(), d_len.data_ptr(), d_first.data_ptr(), nx, nchunks, d_status.data_ptr(),

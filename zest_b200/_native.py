@@ -29,7 +29,7 @@ SYMBOLS = [
     "zg_chunk_order", "zg_dev_hash_chunks_static", "zg_xorb_footer_bytes", "zg_xorb_footer", "zg_dev_int_pipe_peak",
     "zg_dedup_create", "zg_dedup_destroy", "zg_dedup_insert", "zg_dedup_lookup", "zg_dedup_count", "zg_dev_dedup_insert",
     "zg_dev_dedup_lookup", "zg_group_init", "zg_group_shutdown", "zg_group_size", "zg_group_ctx", "zg_partition_xorbs",
-    "zg_group_verify_xorbs",
+    "zg_group_verify_xorbs", "zg_dev_decode_for_hash", "zg_dev_hash_decoded_scratch_bytes", "zg_dev_hash_decoded",
 ]
 
 
@@ -105,6 +105,10 @@ def lib() -> C.CDLL:
         L.zg_dev_decode_scratch_bytes.argtypes = [sz, u64]
         L.zg_dev_decode_scratch_bytes.restype = sz
         L.zg_dev_decode_chunks.argtypes = [vp, vp, u64, vp, sz, vp, u64, vp, vp, sz, vp]
+        L.zg_dev_decode_for_hash.argtypes = [vp, vp, u64, vp, sz, vp, u64, vp, vp, sz, vp]
+        L.zg_dev_hash_decoded_scratch_bytes.argtypes = [u64, sz]
+        L.zg_dev_hash_decoded_scratch_bytes.restype = sz
+        L.zg_dev_hash_decoded.argtypes = [vp, vp, u64, vp, sz, vp, vp, vp, sz, vp]
         L.zg_dev_merkle_scratch_bytes.argtypes = [sz, sz]
         L.zg_dev_merkle_scratch_bytes.restype = sz
         L.zg_dev_merkle.argtypes = [vp, vp, vp, vp, sz, sz, vp, vp, vp, vp, vp, sz, vp]

@@ -199,6 +199,10 @@ struct DeviceScope {
     DeviceScope& operator=(const DeviceScope&) = delete;
 };
 
+__global__ void split_desc_kernel(const ChunkDesc* __restrict__ d, size_t n, uint64_t* __restrict__ off, uint32_t* __restrict__ len) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { off[i] = d[i].dst_off; len[i] = d[i].ulen; }
+}
 }  // namespace
 
 extern "C" {
@@ -575,12 +579,12 @@ int zg_verify_xorbs(zg_ctx* ctx, const uint8_t* const* blobs, const size_t* lens
         cudaEventRecord(L.ev[1], L.st);
         if (e == cudaSuccess)
             e = launch_decode(static_cast<const uint8_t*>(L.comp.p), cpos, reinterpret_cast<ChunkDesc*>(dm), nc, static_cast<uint8_t*>(L.out.p),
-                              ub, reinterpret_cast<int32_t*>(dm + o_status), scr, sz_dec, L.st);
+                              ub, reinterpret_cast<int32_t*>(dm + o_status), scr, sz_dec, L.st, /*keep_planes=*/true);
         cudaEventRecord(L.ev[2], L.st);
         if (e == cudaSuccess)
             e = launch_hash_chunks(static_cast<const uint8_t*>(L.out.p), ub, reinterpret_cast<uint64_t*>(dm + o_off),
                                    reinterpret_cast<uint32_t*>(dm + o_len), nc, make_key(nullptr), dres + r_hashes, scr + sz_dec, sz_hash,
-                                   group, L.st);
+                                   group, L.st, /*planes=*/scr + 256, reinterpret_cast<const ChunkDesc*>(dm));
         cudaEventRecord(L.ev[3], L.st);
         if (e == cudaSuccess)
             e = launch_merkle(dres + r_hashes, reinterpret_cast<uint32_t*>(dm + o_len), nullptr, reinterpret_cast<uint32_t*>(dm + o_first), nx,
@@ -844,6 +848,44 @@ int zg_dev_decode_chunks(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes
     return ZG_OK;
 }
 
+int zg_dev_decode_for_hash(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes, const zg_chunk_desc* d_chunks, size_t n_chunks,
+                           uint8_t* d_out, uint64_t out_bytes, int32_t* d_status, void* d_scratch, size_t scratch_bytes, void* stream) {
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
+    if (r) return r;
+    CU(launch_decode(d_comp, comp_bytes, reinterpret_cast<const ChunkDesc*>(d_chunks), n_chunks, d_out, out_bytes, d_status, d_scratch,
+                     scratch_bytes, static_cast<cudaStream_t>(stream), /*keep_planes=*/true));
+    ctx->kernels += 1;
+    ctx->decoded += out_bytes;
+    return ZG_OK;
+}
+
+size_t zg_dev_hash_decoded_scratch_bytes(uint64_t out_bytes, size_t n) {
+    return align_up(n * 8 + 8, 256) + align_up(n * 4 + 4, 256) + hash_scratch_bytes(out_bytes, n, hash_pick_group(out_bytes));
+}
+
+int zg_dev_hash_decoded(zg_ctx* ctx, const uint8_t* d_out, uint64_t out_bytes, const zg_chunk_desc* d_chunks, size_t n_chunks,
+                        const void* d_decode_scratch, uint8_t* d_hashes, void* d_scratch, size_t scratch_bytes, void* stream) {
+    DeviceScope dev_scope(ctx);
+    int r = dev_scope.rc;
+    if (r) return r;
+    if (n_chunks == 0) return ZG_OK;
+    if (!d_chunks || !d_decode_scratch || !d_hashes || !d_scratch) return fail(ZG_ERR_INVALID_ARG, "null argument");
+    if (scratch_bytes < zg_dev_hash_decoded_scratch_bytes(out_bytes, n_chunks)) return fail(ZG_ERR_CAPACITY, "scratch too small");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint8_t* s = static_cast<uint8_t*>(d_scratch);
+    const ChunkDesc* dc = reinterpret_cast<const ChunkDesc*>(d_chunks);
+    uint64_t* off = reinterpret_cast<uint64_t*>(s);
+    uint32_t* len = reinterpret_cast<uint32_t*>(s + align_up(n_chunks * 8 + 8, 256));
+    const size_t o_hash = align_up(n_chunks * 8 + 8, 256) + align_up(n_chunks * 4 + 4, 256);
+    split_desc_kernel<<<(unsigned)((n_chunks + 255) / 256), 256, 0, st>>>(dc, n_chunks, off, len);
+    CU(launch_hash_chunks(d_out, out_bytes, off, len, n_chunks, make_key(nullptr), d_hashes, s + o_hash, scratch_bytes - o_hash,
+                          hash_pick_group(out_bytes), st, static_cast<const uint8_t*>(d_decode_scratch) + 256, dc));
+    ctx->kernels += 6;
+    ctx->hashed += n_chunks;
+    return ZG_OK;
+}
+
 size_t zg_dev_merkle_scratch_bytes(size_t n_chunks, size_t n_xorbs) { return merkle_scratch_bytes(n_chunks, n_xorbs); }
 
 int zg_dev_merkle(zg_ctx* ctx, const uint8_t* d_hashes, const uint32_t* d_lens, const uint32_t* d_first, size_t n_xorbs, size_t n_chunks,
@@ -873,10 +915,6 @@ VerifyLayout verify_layout(size_t nc, size_t nx, uint64_t out_bytes) {
     v.total = o + align_up((size_t)out_bytes + 16, 256);  // decoded bytes live at the end of the scratch
     return v;
 }
-__global__ void split_desc_kernel(const ChunkDesc* __restrict__ d, size_t n, uint64_t* __restrict__ off, uint32_t* __restrict__ len) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { off[i] = d[i].dst_off; len[i] = d[i].ulen; }
-}
 }  // namespace
 
 size_t zg_dev_verify_scratch_bytes(size_t n_chunks, size_t n_xorbs, uint64_t out_bytes) { return verify_layout(n_chunks, n_xorbs, out_bytes).total; }
@@ -899,8 +937,10 @@ int zg_dev_verify_xorbs(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_bytes,
     int32_t* status = reinterpret_cast<int32_t*>(s + v.status);
     uint8_t* decoded = s + (v.total - align_up((size_t)out_bytes + 16, 256));
     if (n_chunks) split_desc_kernel<<<(unsigned)((n_chunks + 255) / 256), 256, 0, st>>>(dc, n_chunks, off, len);
-    CU(launch_decode(d_comp, comp_bytes, dc, n_chunks, decoded, out_bytes, status, s + v.dec, v.hash - v.dec, st));
-    CU(launch_hash_chunks(decoded, out_bytes, off, len, n_chunks, make_key(nullptr), d_chunk_hashes, s + v.hash, v.mer - v.hash, v.group, st));
+    // verify only hashes the decoded bytes: byte-grouped chunks stay as planes and the hash regroups them as it reads
+    CU(launch_decode(d_comp, comp_bytes, dc, n_chunks, decoded, out_bytes, status, s + v.dec, v.hash - v.dec, st, /*keep_planes=*/true));
+    CU(launch_hash_chunks(decoded, out_bytes, off, len, n_chunks, make_key(nullptr), d_chunk_hashes, s + v.hash, v.mer - v.hash, v.group, st,
+                          /*planes=*/s + v.dec + 256, dc));
     CU(launch_merkle(d_chunk_hashes, len, nullptr, d_first, n_xorbs, n_chunks, status, d_expected, d_roots, d_verdict, s + v.mer,
                      v.off - v.mer, st));
     ctx->kernels += 8;

@@ -168,22 +168,76 @@ __device__ __noinline__ void load_block_general(const uint8_t* p, uint32_t blen,
     }
 }
 
+// One 64-byte block of a chunk that is still BYTE-GROUPED (scheme 2 as the decoder leaves it when only the hash is wanted:
+// plane k = the chunk's bytes at index = k mod 4, the four planes back to back).  Output byte 4j + k of the
+// chunk is plane_k[j], so block bytes boff .. boff+63 are 16 consecutive bytes of each plane, interleaved: four unaligned
+// 16-byte reads and a 4 x 4 byte transpose per group of four words -- ~80 instructions on top of a 784-instruction
+// compression, against a separate regroup pass over the whole chunk in the decoder (17 % of its time on bf16).
+// pl = the chunk's planes (16-byte aligned), n = the chunk's length, blen = bytes of the block that exist (zero beyond).
+__device__ __forceinline__ void load_block_planar(const uint8_t* pl, uint32_t n, uint32_t boff, uint32_t blen, uint32_t (&m)[16]) {
+    const uint32_t q = n >> 2, r = n & 3u;
+    const uint32_t pstart[4] = {0u, q + (0u < r), 2u * q + (0u < r) + (1u < r), 3u * q + (0u < r) + (1u < r) + (2u < r)};
+    const uint32_t j0 = boff >> 2;
+    uint32_t w[4][4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        // 16 bytes of plane k from any alignment: the two aligned 16-byte vectors that hold them (the second one is the
+        // next block's first: an L1 hit), shifted by whole words with two levels of selects and by bytes with a funnel
+        // shift.  Reads stay inside the chunk's 16-byte padded storage plus the 16 bytes of slack behind the buffer.
+        const uintptr_t a = reinterpret_cast<uintptr_t>(pl) + pstart[k] + j0;
+        const uint4* vp = reinterpret_cast<const uint4*>(a & ~(uintptr_t)15);
+        const uint32_t mis = (uint32_t)(a & 15), ws = mis >> 2, bs = (mis & 3u) * 8;
+        const bool any = blen > (uint32_t)k;  // plane k has bytes in this block
+        uint4 lo = make_uint4(0, 0, 0, 0), hi = make_uint4(0, 0, 0, 0);
+        if (any) { lo = vp[0]; if (mis) hi = vp[1]; }
+        uint32_t v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+        if (ws & 2) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) v[i] = v[i + 2];
+        }
+        if (ws & 1) {
+#pragma unroll
+            for (int i = 0; i < 5; i++) v[i] = v[i + 1];
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) w[k][i] = __funnelshift_r(v[i], v[i + 1], bs);
+    }
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+        const uint32_t a = w[0][g], b = w[1][g], c = w[2][g], d = w[3][g];
+        const uint32_t t0 = __byte_perm(a, b, 0x5140), t1 = __byte_perm(a, b, 0x7362);
+        const uint32_t u0 = __byte_perm(c, d, 0x5140), u1 = __byte_perm(c, d, 0x7362);
+        m[4 * g] = __byte_perm(t0, u0, 0x5410); m[4 * g + 1] = __byte_perm(t0, u0, 0x7632);
+        m[4 * g + 2] = __byte_perm(t1, u1, 0x5410); m[4 * g + 3] = __byte_perm(t1, u1, 0x7632);
+    }
+    if (blen < 64u) {  // the chunk ends inside this block: what lies beyond (the next plane's bytes, padding) reads as zero
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const int valid = (int)blen - 4 * i;
+            m[i] &= valid >= 4 ? 0xffffffffu : (valid <= 0 ? 0u : ((1u << (8 * valid)) - 1u));
+        }
+    }
+}
+
 // ---- leaf kernel: one thread = one aligned group of G leaves ------------------------------------------------
-template <int G, bool FMA_ADDS>
+template <int G, bool FMA_ADDS, bool PLANAR>
 __global__ void __launch_bounds__(128) hash_leaf_kernel(const uint8_t* __restrict__ data,
                                                         const uint64_t* __restrict__ off,
                                                         const uint32_t* __restrict__ len, const B3Key key,
                                                         const uint32_t* __restrict__ P,
                                                         const uint32_t* __restrict__ map,
                                                         const uint32_t* __restrict__ total_slots,
-                                                        uint4* __restrict__ nodes, uint4* __restrict__ out) {
+                                                        uint4* __restrict__ nodes, uint4* __restrict__ out,
+                                                        const uint8_t* __restrict__ planes,
+                                                        const ChunkDesc* __restrict__ descs) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= *total_slots) return;
     uint32_t ci = map[t];
     if (ci == 0xffffffffu) return;  // slot of a chunk that did not fit the scratch (hash_map_kernel)
     uint32_t k = t - P[ci];
     uint64_t clen = chunk_len(off, len, ci);
-    const uint8_t* base = data + off[ci];
+    const bool planar = PLANAR && descs[ci].scheme == 2;  // still byte-grouped: read the planes, regroup on the fly
+    const uint8_t* base = (planar ? planes : data) + off[ci];
     uint32_t n_leaves = clen == 0 ? 1u : (uint32_t)((clen + kLeaf - 1) / kLeaf);
     uint32_t first_leaf = k * G;
     uint32_t g = n_leaves - first_leaf < (uint32_t)G ? n_leaves - first_leaf : (uint32_t)G;
@@ -209,7 +263,8 @@ __global__ void __launch_bounds__(128) hash_leaf_kernel(const uint8_t* __restric
         for (uint32_t b = 0; b < nblk; b++) {
             uint32_t blen = llen - 64 * b < 64 ? llen - 64 * b : 64;
             uint32_t m[16];
-            if (fast_align && blen == 64) load_block_aligned(p + 64 * b, m);
+            if (planar) load_block_planar(base, (uint32_t)clen, (uint32_t)lo + 64 * b, blen, m);
+            else if (fast_align && blen == 64) load_block_aligned(p + 64 * b, m);
             else load_block_general(p + 64 * b, blen, m);
             uint32_t fl = key.base_flags | (b == 0 ? B3_CHUNK_START : 0u) |
                           (b == nblk - 1 ? (B3_CHUNK_END | root_leaf) : 0u);
@@ -329,7 +384,7 @@ size_t hash_scratch_bytes(uint64_t data_bytes, size_t n, int group) { return has
 
 cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const uint64_t* off, const uint32_t* len,
                                size_t n, const B3Key& key, uint8_t* out, void* scratch, size_t scratch_bytes,
-                               int group, cudaStream_t st) {
+                               int group, cudaStream_t st, const uint8_t* planes, const ChunkDesc* descs) {
     if (n == 0) return cudaSuccess;
     if (group != 1 && group != 2 && group != 4 && group != 8) return cudaErrorInvalidValue;
     HashLayout L = hash_layout(data_bytes, n, group);
@@ -346,10 +401,12 @@ cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const u
     hash_map_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(off, len, n, gb, P, tiles, (uint32_t)L.slots_cap, map, o4);
     unsigned blocks = (unsigned)((L.slots_cap + 127) / 128);
     static const bool fma_adds = []() { const char* e = getenv("ZEST_B3_PLAIN_ADDS"); return !(e && e[0] == '1'); }();
-#define ZG_LEAF(G)                                                                                                    \
-    do {                                                                                                              \
-        if (fma_adds) hash_leaf_kernel<G, true><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4); \
-        else hash_leaf_kernel<G, false><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4);        \
+    const bool planar = planes != nullptr && descs != nullptr;
+#define ZG_LEAF(G)                                                                                                                         \
+    do {                                                                                                                                   \
+        if (planar) hash_leaf_kernel<G, true, true><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4, planes, descs); \
+        else if (fma_adds) hash_leaf_kernel<G, true, false><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4, nullptr, nullptr); \
+        else hash_leaf_kernel<G, false, false><<<blocks, 128, 0, st>>>(data, off, len, key, P, map, P + n, nodes, o4, nullptr, nullptr); \
     } while (0)
     switch (group) {
         case 1: ZG_LEAF(1); break;

@@ -31,9 +31,12 @@ size_t hash_scratch_bytes(uint64_t data_bytes, size_t n_chunks, int group);
 // Hash n chunks.  Chunk i = data[off[i] .. off[i] + len_i), len_i = len ? len[i] : off[i+1] - off[i].
 // data must be 16-byte aligned and readable up to the next multiple of 16 past the last chunk.
 // out: n x 32 bytes.  scratch: hash_scratch_bytes(data_bytes, n, group) bytes, 256-byte aligned.
+struct ChunkDesc;
+// planes + descs (both or neither): chunk i with descs[i].scheme == 2 is read from planes + off[i], still byte-grouped as
+// the decoder left it (launch_decode with keep_planes), and regrouped on the fly; every other chunk from data + off[i].
 cudaError_t launch_hash_chunks(const uint8_t* data, uint64_t data_bytes, const uint64_t* off, const uint32_t* len,
                                size_t n, const B3Key& key, uint8_t* out, void* scratch, size_t scratch_bytes,
-                               int group, cudaStream_t st);
+                               int group, cudaStream_t st, const uint8_t* planes = nullptr, const ChunkDesc* descs = nullptr);
 
 // ---------------------------------------------------------------------------------------------- merkle
 // One fold job per xorb: chunks [first[x], first[x+1]) of hashes/lens -> roots[x]; verdict from status/expected.
@@ -55,8 +58,11 @@ struct ChunkDesc {      // one per chunk, built by the host walk (zg_xorb_index)
 // Fill chunks[t].order so that work is handed out longest-first (keeps the last warps from finishing alone).
 void fill_decode_order(ChunkDesc* chunks, size_t n);
 size_t decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes);
+// keep_planes: scheme-2 chunks are left byte-grouped in the plane buffer (scratch + 256, at their dst_off) instead of being
+// regrouped into out -- for a caller that only hashes them (launch_hash_chunks with planes).
 cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkDesc* chunks, size_t n, uint8_t* out,
-                          uint64_t out_bytes, int32_t* status, void* scratch, size_t scratch_bytes, cudaStream_t st);
+                          uint64_t out_bytes, int32_t* status, void* scratch, size_t scratch_bytes, cudaStream_t st,
+                          bool keep_planes = false);
 
 // ---------------------------------------------------------------------------------------------- cdc
 size_t cdc_scratch_bytes(uint64_t len);

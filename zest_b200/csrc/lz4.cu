@@ -517,7 +517,7 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
 #endif
 __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8_t* __restrict__ comp, const ChunkDesc* __restrict__ chunks,
                                                         uint32_t n_chunks, uint8_t* out, uint8_t* tmp,
-                                                        int32_t* __restrict__ status, uint32_t* ticket, const uint8_t* comp_hi) {
+                                                        int32_t* __restrict__ status, uint32_t* ticket, const uint8_t* comp_hi, uint32_t keep_planes) {
     __shared__ __align__(16) WarpShared ws;
     const uint32_t lane = threadIdx.x;
     const uint8_t* const win = reinterpret_cast<const uint8_t*>(ws.win);
@@ -863,7 +863,7 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
         // ---- chunk finished this round: regroup (scheme 2) and publish the status
         if (finished) {
             __syncwarp();
-            if (err == 0 && scheme == 2) warp_regroup(fin_out, lz, ulen, lane);
+            if (err == 0 && scheme == 2 && !keep_planes) warp_regroup(fin_out, lz, ulen, lane);
 #ifdef ZG_DIAG_HASH_LOAD  // timing experiment only: integer work of the size and shape a BLAKE3 of the chunk would be
             {             // (784 thread-instructions per 64 bytes per lane, four independent columns, add / xor / rotate), no loads
                 uint32_t va[4], vb[4], vc[4], vd[4];
@@ -923,7 +923,7 @@ size_t decode_scratch_bytes(size_t n_chunks, uint64_t out_bytes) {
 }
 
 cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkDesc* chunks, size_t n, uint8_t* out,
-                          uint64_t out_bytes, int32_t* status, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+                          uint64_t out_bytes, int32_t* status, void* scratch, size_t scratch_bytes, cudaStream_t st, bool keep_planes) {
     if (n == 0) return cudaSuccess;
     if (scratch_bytes < decode_scratch_bytes(n, out_bytes) || n >= 0xffffffffull) return cudaErrorInvalidValue;
     uint8_t* sb = static_cast<uint8_t*>(scratch);
@@ -949,7 +949,7 @@ cudaError_t launch_decode(const uint8_t* comp, uint64_t comp_bytes, const ChunkD
     if (const char* v = getenv("ZEST_LZ4_WARPS")) { long w = atol(v); if (w > 0) warps = (size_t)w; }
     if (warps > n) warps = n;
     const uint8_t* comp_hi = comp + align_up((size_t)comp_bytes, 16);
-    lz4_decode_kernel<<<(unsigned)warps, 32, 0, st>>>(comp, chunks, (uint32_t)n, out, tmp, status, ticket, comp_hi);
+    lz4_decode_kernel<<<(unsigned)warps, 32, 0, st>>>(comp, chunks, (uint32_t)n, out, tmp, status, ticket, comp_hi, keep_planes ? 1u : 0u);
     return cudaGetLastError();
 }
 
