@@ -496,8 +496,10 @@ __device__ __forceinline__ void exec_group(const uint8_t* src, const uint8_t* wi
     const long long pt2 = clock64();
     ZG_PF(1, pt2 - pt1);
 #endif
+#ifndef ZG_DIAG_NO_ROUNDS  // (timing experiment: the matches that read the step's own output are not copied)
 #pragma unroll
     for (int q = 0; q < NP; q++) match_rounds(lz, dst[q] + lit[q], ml[q], off[q], lane);
+#endif
 #ifdef ZG_LZ4_PROFILE
     ZG_PF(2, clock64() - pt2);
 #endif
@@ -662,7 +664,9 @@ __global__ void __launch_bounds__(32, ZG_MIN_CTAS) lz4_decode_kernel(const uint8
                     }
                     gop += adv;
                 }
+#ifndef ZG_DIAG_NO_EXEC  // (timing experiment: parse, place and check the sequences, copy nothing)
                 exec_group<kNP, true>(src, win, lz, step0, lit_src, lit_w, lit, ml, off, dst, lane);
+#endif
 #ifdef ZG_LZ4_PROFILE
                 for (int q = 0; q < kNP; q++) n_true += __popc(__ballot_sync(kFull, (lit[q] | ml[q]) != 0));
 #endif
