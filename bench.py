@@ -16,9 +16,10 @@ GPU.  Rank 0 prints ONE JSON line.
               would); `e2e.pageable`: the same call on ordinary malloc'ed blobs (what an unmodified zest allocator
               hands over).  The streaming workload replaces the single call by producer threads -> pinned ring ->
               consumer threads (see stream_e2e).
-  roofline    the dominant kernel of the step (timed alone with CUDA events, same inputs), algorithmic bytes /
-              time against the measured HBM copy bandwidth in MEASURED_PEAKS.json; `stages` lists every kernel;
-              `blake3_alu` reports the hash kernel against the integer-ALU roof.
+  roofline    the dominant kernel of the step (timed alone with CUDA events, same inputs, as the verify call runs it:
+              zg_dev_decode_for_hash / zg_dev_hash_decoded / zg_dev_merkle), algorithmic bytes / time against the
+              measured HBM copy bandwidth in MEASURED_PEAKS.json; `stages` lists every kernel; `blake3_alu` reports the
+              hash kernel against the integer-ALU roof.
   cpu_baseline  the CPU oracle (oracle/, a port -- the reference's zig-xet code cannot be built here) on all host
               cores over a bounded sample of the same xorbs; rows C1-C6 of BASELINE.md section 3 where they apply.
   --impl reference   times only that CPU arm and prints it in the same shape.
