@@ -860,8 +860,17 @@ int zg_dev_decode_for_hash(zg_ctx* ctx, const uint8_t* d_comp, uint64_t comp_byt
     return ZG_OK;
 }
 
+namespace {
+// Leaves per thread for the hash that reads byte-grouped chunks as planes: four strided streams per thread instead of one,
+// so at most 4 KiB per thread (measured at 8 GB: G = 8 / 4 / 2 -> 5.40 / 5.18 / 5.19 ms).
+int planar_group(uint64_t out_bytes) {
+    const int g = hash_pick_group(out_bytes);
+    return g > 4 ? 4 : g;
+}
+}  // namespace
+
 size_t zg_dev_hash_decoded_scratch_bytes(uint64_t out_bytes, size_t n) {
-    return align_up(n * 8 + 8, 256) + align_up(n * 4 + 4, 256) + hash_scratch_bytes(out_bytes, n, hash_pick_group(out_bytes));
+    return align_up(n * 8 + 8, 256) + align_up(n * 4 + 4, 256) + hash_scratch_bytes(out_bytes, n, planar_group(out_bytes));
 }
 
 int zg_dev_hash_decoded(zg_ctx* ctx, const uint8_t* d_out, uint64_t out_bytes, const zg_chunk_desc* d_chunks, size_t n_chunks,
@@ -880,7 +889,7 @@ int zg_dev_hash_decoded(zg_ctx* ctx, const uint8_t* d_out, uint64_t out_bytes, c
     const size_t o_hash = align_up(n_chunks * 8 + 8, 256) + align_up(n_chunks * 4 + 4, 256);
     split_desc_kernel<<<(unsigned)((n_chunks + 255) / 256), 256, 0, st>>>(dc, n_chunks, off, len);
     CU(launch_hash_chunks(d_out, out_bytes, off, len, n_chunks, make_key(nullptr), d_hashes, s + o_hash, scratch_bytes - o_hash,
-                          hash_pick_group(out_bytes), st, static_cast<const uint8_t*>(d_decode_scratch) + 256, dc));
+                          planar_group(out_bytes), st, static_cast<const uint8_t*>(d_decode_scratch) + 256, dc));
     ctx->kernels += 6;
     ctx->hashed += n_chunks;
     return ZG_OK;
@@ -904,7 +913,7 @@ namespace {
 struct VerifyLayout { size_t dec, hash, mer, off, len, status, total; int group; };
 VerifyLayout verify_layout(size_t nc, size_t nx, uint64_t out_bytes) {
     VerifyLayout v;
-    v.group = hash_pick_group(out_bytes);
+    v.group = planar_group(out_bytes);
     size_t o = 0;
     v.dec = o; o += align_up(decode_scratch_bytes(nc, out_bytes), 256);
     v.hash = o; o += align_up(hash_scratch_bytes(out_bytes, nc, v.group), 256);
