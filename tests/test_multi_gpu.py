@@ -135,3 +135,38 @@ def test_group_on_two_gpus_uses_both():
     assert r.ok and s0["h2d_bytes"] > 0 and s1["h2d_bytes"] > 0
     parts = z.partition_native([len(b) for b in blobs], 2)
     assert abs(s0["h2d_bytes"] - sum(len(blobs[i]) for i in parts[0])) < 200_000
+
+
+@pytest.mark.gpu
+def test_calls_leave_the_callers_device_alone():
+    """A context on device 1 used from a thread whose current device is 0 (torch on cuda:0 next to a context elsewhere,
+    a zg_group worker next to its caller): every entry point works on its context's device and puts the thread's
+    device back -- checked through the CUDA runtime torch itself uses."""
+    import ctypes as C
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import zest_b200 as z
+    from oracle import xet_oracle as oz
+    rt = C.CDLL("libcudart.so.12")
+
+    def current():
+        d = C.c_int(-1)
+        assert rt.cudaGetDevice(C.byref(d)) == 0
+        return d.value
+    torch.cuda.set_device(0)
+    torch.zeros(1, device="cuda:0")
+    assert current() == 0
+    ctx = z.Context(1)
+    assert current() == 0
+    data = oz.synth_zipf_text(600_000, 3)
+    xs, ends, hashes = oz.make_xorbs(data, 1)
+    r = z.verify_xorbs([xs[0].blob], [xs[0].expected], ctx=ctx)
+    assert r.ok and current() == 0
+    assert z.XorbReader(xs[0].blob, ctx).extract_chunk_range(0, xs[0].n_chunks) == data.tobytes() and current() == 0
+    assert np.array_equal(z.cdc(data, ctx=ctx), oz.cdc(data)) and current() == 0
+    p = ctx.pinned_empty(4096)
+    ctx.pinned_free(p)
+    assert ctx.stats()["h2d_bytes"] > 0 and current() == 0
+    ctx.close()
+    assert current() == 0

@@ -217,6 +217,13 @@ int zg_init(int device, const zg_opts* opts, zg_ctx** out) {
         return fail(ZG_ERR_NO_DEVICE, "no CUDA device (%s); libzest_gpu has no CPU path", e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
     }
     if (device < 0 || device >= count) return fail(ZG_ERR_INVALID_ARG, "device %d out of range (0..%d)", device, count - 1);
+    // work on `device`, then put the calling thread's device back (whatever way this function is left)
+    struct Restore {
+        int prev = -1;
+        ~Restore() { if (prev >= 0) cudaSetDevice(prev); }
+    } restore;
+    if (cudaGetDevice(&restore.prev) != cudaSuccess) { (void)cudaGetLastError(); restore.prev = -1; }
+    if (restore.prev == device) restore.prev = -1;
     CU(cudaSetDevice(device));
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
@@ -237,7 +244,7 @@ int zg_init(int device, const zg_opts* opts, zg_ctx** out) {
 
 void zg_shutdown(zg_ctx* c) {
     if (!c) return;
-    cudaSetDevice(c->device);
+    DeviceScope dev_scope(c);
     for (auto& l : c->lanes) {
         if (l.st) cudaStreamSynchronize(l.st);
         l.comp.release(); l.out.release(); l.meta.release(); l.res.release(); l.scratch.release();
